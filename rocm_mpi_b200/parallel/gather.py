@@ -1,0 +1,63 @@
+"""``gather``: assemble equally-shaped local blocks into one global array on the root rank.
+
+Reference call sites: ``gather!(T_nh, T_v)`` at ``scripts/diffusion_2D_ap.jl:46`` (also
+``kp.jl:95``, ``perf.jl:61``, ``perf_hide.jl:114``), always with the halo-free interior
+``T[2:end-1,2:end-1]`` so that blocks abut exactly and the global array has
+``(n-2)*dims`` points per dimension (``ap.jl:31-33``).  The block of the rank with Cartesian
+coordinates ``(cx, cy, cz)`` lands at ``[cx*lx:(cx+1)*lx, cy*ly:..., cz*lz:...]``.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from .grid import global_grid
+from .topology import cart_coords
+
+__all__ = ["gather", "inner", "gather_interior"]
+
+
+def inner(A: torch.Tensor) -> torch.Tensor:
+    """Halo-free interior view: ``A[1:-1, 1:-1(, 1:-1)]`` over every dimension of size > 2."""
+    sl = tuple(slice(1, -1) if s > 2 else slice(None) for s in A.shape)
+    return A[sl]
+
+
+def gather(A_local: torch.Tensor, A_global: Optional[torch.Tensor], root: int = 0) -> None:
+    """Gather ``A_local`` from every rank into ``A_global`` on ``root``.
+
+    ``A_global`` only needs to exist on the root (pass ``None`` elsewhere).  Device tensors
+    are accepted; they are brought to the host first, as the reference does with
+    ``Array(T[2:end-1,2:end-1])`` (``scripts/diffusion_2D_ap.jl:45``).
+    """
+    g = global_grid()
+    block = A_local.detach()
+    if block.is_cuda:
+        block = block.contiguous().cpu()
+    blocks = g.comm.gather_blocks(block.contiguous(), root)
+    if g.me != root:
+        return
+    if A_global is None:
+        raise ValueError("A_global must be provided on the root rank")
+    lshape = tuple(block.shape)
+    nd = len(lshape)
+    want = tuple(lshape[d] * g.dims[d] for d in range(nd))
+    if tuple(A_global.shape) != want:
+        raise ValueError(f"A_global has shape {tuple(A_global.shape)}, expected {want}")
+    for r, blk in enumerate(blocks):
+        c = cart_coords(r, g.dims)
+        sl = tuple(slice(c[d] * lshape[d], (c[d] + 1) * lshape[d]) for d in range(nd))
+        A_global[sl].copy_(blk)
+
+
+def gather_interior(A: torch.Tensor, root: int = 0) -> Optional[torch.Tensor]:
+    """Convenience: strip the halo, gather, and return the global array on the root."""
+    g = global_grid()
+    blk = inner(A)
+    out = None
+    if g.me == root:
+        out = torch.zeros(tuple(blk.shape[d] * g.dims[d] for d in range(blk.dim())),
+                          dtype=A.dtype)
+    gather(blk, out, root)
+    return out

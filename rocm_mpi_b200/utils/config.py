@@ -1,0 +1,83 @@
+"""Run configuration.
+
+The reference hard-codes everything as script constants (``lx, ly, lam, Cp0`` at
+``scripts/diffusion_2D_ap.jl:11-13``, ``nx, ny, nt`` at ``:15-16``, ``threads``/``grid`` at
+``scripts/diffusion_2D_kp.jl:63-64``, ``fact`` at ``scripts/diffusion_2D_perf.jl:21``, ``b_width`` at
+``scripts/diffusion_2D_perf_hide.jl:42``, ``do_vis`` kwarg at ``scripts/diffusion_2D_perf.jl:15``) and
+selects variants by (un)commenting lines (``scripts/runme.sh:5-9``).  Here they are fields of a
+dataclass that can be filled from the command line or from ``IGG_B200_*`` environment variables.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+from dataclasses import dataclass, field, fields
+from typing import Optional, Tuple
+
+__all__ = ["DiffusionConfig", "add_config_args", "config_from_args", "env_flag"]
+
+
+def env_flag(name: str, default: bool = False) -> bool:
+    v = os.environ.get(name)
+    if v is None:
+        return default
+    return v.strip().lower() not in ("0", "false", "no", "off", "")
+
+
+@dataclass
+class DiffusionConfig:
+    # physics (reference scripts/diffusion_2D_ap.jl:11-13)
+    lx: float = 10.0
+    ly: float = 10.0
+    lz: float = 10.0
+    lam: float = 1.0
+    Cp0: float = 1.0
+    # numerics: LOCAL sizes including the overlap (reference scripts/diffusion_2D_ap.jl:15-16)
+    nx: int = 128
+    ny: int = 128
+    nz: int = 1
+    nt: int = 1000
+    warmup: int = 10              # iterations excluded from timing (reference perf.jl:48)
+    # decomposition
+    dimx: int = 0
+    dimy: int = 0
+    dimz: int = 0
+    periodx: int = 0
+    periody: int = 0
+    periodz: int = 0
+    # variant-specific
+    b_width: Tuple[int, int, int] = (16, 4, 4)   # hide_communication boundary width
+    transport: Optional[str] = None              # peer | nccl | host | gloo (None = default)
+    kernel: str = "tma"                          # tma | direct  (stencil kernel flavour)
+    fused: bool = True                           # fuse the halo push into the stencil kernel
+    device_type: str = "auto"
+    # output
+    do_vis: bool = True
+    outdir: str = "output"
+    quiet: bool = False
+
+    def __post_init__(self):
+        if self.transport is None:
+            self.transport = os.environ.get("IGG_B200_TRANSPORT") or None
+        bw = tuple(int(b) for b in self.b_width)
+        self.b_width = bw + (bw[-1],) * (3 - len(bw))
+
+
+def add_config_args(p: argparse.ArgumentParser, defaults: Optional[DiffusionConfig] = None) -> None:
+    d = defaults or DiffusionConfig()
+    for f in fields(DiffusionConfig):
+        v = getattr(d, f.name)
+        flag = "--" + f.name.replace("_", "-")
+        if f.name == "b_width":
+            p.add_argument(flag, type=int, nargs="+", default=list(v))
+        elif isinstance(v, bool):
+            p.add_argument(flag, type=lambda s: s.lower() not in ("0", "false", "no"), default=v)
+        elif v is None:
+            p.add_argument(flag, type=str, default=None)
+        else:
+            p.add_argument(flag, type=type(v), default=v)
+
+
+def config_from_args(ns: argparse.Namespace) -> DiffusionConfig:
+    kw = {f.name: getattr(ns, f.name) for f in fields(DiffusionConfig) if hasattr(ns, f.name)}
+    return DiffusionConfig(**kw)

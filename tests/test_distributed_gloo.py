@@ -1,0 +1,28 @@
+"""Multi-process CPU tests (gloo): halo exchange, gather and the ap application."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import pytest
+
+from mp_util import run_workers
+
+
+@pytest.mark.parametrize("args,nprocs", [
+    ((8, 7, 1, 0, 0, 0, 0, 0, 0), 4),      # 2x2
+    ((8, 7, 1, 1, 2, 0, 1, 1, 0), 2),      # 1x2 periodic both (self-neighbour in x, same rank both sides in y)
+    ((6, 5, 4, 0, 0, 0, 0, 1, 0), 4),      # 3-D 2x2x1... dims_create -> (2,2,1), periodic y
+    ((6, 5, 4, 1, 1, 2, 0, 0, 1), 2),      # 3-D split in z, periodic z
+])
+def test_update_halo_gather_gloo(args, nprocs):
+    outs = run_workers("halo_gloo.py", nprocs, args)
+    assert all("ok" in o for o in outs)
+
+
+def test_ap_app_4_ranks_bit_exact(tmp_path):
+    # BASELINE.json config 1 at reduced step count (the full 1000-step golden run is in test_oracle)
+    outs = run_workers("ap_gloo.py", 4, (128, 128, 0, 0, 100, str(tmp_path)))
+    assert all("ok" in o for o in outs)
+
+
+def test_ap_app_8_ranks_4x2_layout(tmp_path):
+    outs = run_workers("ap_gloo.py", 8, (65, 128, 4, 2, 40, str(tmp_path)), timeout=600)
+    assert all("ok" in o for o in outs)

@@ -1,0 +1,60 @@
+"""update_halo semantics on the virtual-rank model (no processes, no GPU)."""
+import torch
+
+from rocm_mpi_b200.parallel.halo import halo_planes
+from rocm_mpi_b200.parallel.virtual import VirtualGrid
+
+
+def test_halo_planes_indices():
+    specs = halo_planes((8, 6, 1), (2, 2, 2), (8, 6))
+    assert specs[0].send == (1, 6) and specs[0].recv == (0, 7)
+    assert specs[1].send == (1, 4) and specs[1].recv == (0, 5)
+    assert specs[2] is None
+    # staggered (n+1): overlap 3 -> planes 2 and size-3
+    specs = halo_planes((8, 6, 1), (2, 2, 2), (9, 6))
+    assert specs[0].send == (2, 6) and specs[0].recv == (0, 8)
+    # staggered (n-1): overlap 1 -> skipped in that dim
+    specs = halo_planes((8, 6, 1), (2, 2, 2), (7, 6))
+    assert specs[0] is None and specs[1] is not None
+
+
+def test_corner_propagation_2x2():
+    vg = VirtualGrid((6, 5), (2, 2))
+    locs = [torch.full((6, 5), float(r)) for r in range(4)]
+    for r in range(4):
+        locs[r][1:-1, 1:-1] = 10.0 * (r + 1)
+    vg.update_halo(locs)
+    # rank 0 at coords (0,0): high-x neighbour is rank 2, high-y neighbour rank 1, diagonal rank 3
+    assert torch.all(locs[0][5, 1:4] == 30.0)
+    assert torch.all(locs[0][1:5, 4] == 20.0)
+    assert locs[0][5, 4] == 40.0             # corner value came from the diagonal neighbour
+    assert locs[0][0, 0] == 0.0              # global boundary untouched
+    assert locs[3][0, 0] == 10.0
+
+
+def test_periodic_self_neighbor():
+    vg = VirtualGrid((6, 5), (1, 1), periods=(1, 0))
+    A = torch.arange(30, dtype=torch.float64).reshape(6, 5)
+    ref = A.clone()
+    vg.update_halo([A])
+    assert torch.equal(A[0], ref[4]) and torch.equal(A[5], ref[1])
+    assert torch.equal(A[1:5], ref[1:5])
+
+
+def test_3d_global_consistency():
+    # after one update_halo every overlapping cell pair holds the same value
+    vg = VirtualGrid((6, 5, 4), (2, 2, 2))
+    G = torch.arange(10 * 8 * 6, dtype=torch.float64).reshape(10, 8, 6)
+    locs = vg.scatter(G)
+    for r, L in enumerate(locs):      # scramble halos, keep interiors
+        keep = L[1:-1, 1:-1, 1:-1].clone()
+        L.fill_(-1.0)
+        L[1:-1, 1:-1, 1:-1] = keep
+    vg.update_halo(locs)
+    for r, L in enumerate(locs):
+        o = vg.origin(r)
+        want = G[o[0]:o[0] + 6, o[1]:o[1] + 5, o[2]:o[2] + 4]
+        interior_of_global = torch.zeros_like(G, dtype=torch.bool)
+        interior_of_global[1:-1, 1:-1, 1:-1] = True
+        m = interior_of_global[o[0]:o[0] + 6, o[1]:o[1] + 5, o[2]:o[2] + 4]
+        assert torch.equal(L[m], want[m])
