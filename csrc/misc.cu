@@ -1,0 +1,237 @@
+// Small device-side utilities: initial condition, plane pack/unpack, interior extraction,
+// max/sum reduction, colour mapping.
+#include "common.cuh"
+
+namespace {
+using namespace igg;
+
+// ---- initial condition (reference scripts/diffusion_2D_ap.jl:28: host comprehension + upload) ---------
+__global__ void gaussian_ic2d_kernel(double* __restrict__ T, int nx, int ny, double x0, double y0, double dx,
+                                     double dy, double lx, double ly) {
+    const int iy = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ix = blockIdx.y * blockDim.y + threadIdx.y;
+    if (ix < nx && iy < ny) {
+        const double x = (x0 + ix * dx) + dx / 2 - lx / 2;
+        const double y = (y0 + iy * dy) + dy / 2 - ly / 2;
+        T[(size_t)ix * ny + iy] = exp(-(x * x) - (y * y));
+    }
+}
+
+__global__ void gaussian_ic3d_kernel(double* __restrict__ T, int nx, int ny, int nz, double x0, double y0,
+                                     double z0, double dx, double dy, double dz, double lx, double ly, double lz) {
+    const int iz = blockIdx.x * blockDim.x + threadIdx.x;
+    const int iy = blockIdx.y * blockDim.y + threadIdx.y;
+    const int ix = blockIdx.z;
+    if (ix < nx && iy < ny && iz < nz) {
+        const double x = (x0 + ix * dx) + dx / 2 - lx / 2;
+        const double y = (y0 + iy * dy) + dy / 2 - ly / 2;
+        const double z = (z0 + iz * dz) + dz / 2 - lz / 2;
+        T[((size_t)ix * ny + iy) * nz + iz] = exp(-(x * x) - (y * y) - (z * z));
+    }
+}
+
+// ---- plane pack / unpack ----------------------------------------------------------------------------
+// plane of dimension `dim` at `idx`: elements (a, b) over the two remaining dimensions, enumerated in
+// row-major order of the remaining dimensions.
+__device__ __forceinline__ size_t plane_elem(int n0, int n1, int n2, int dim, int idx, size_t e) {
+    if (dim == 0) return (size_t)idx * n1 * n2 + e;                       // contiguous block
+    if (dim == 1) { const size_t a = e / n2, c = e % n2; return (a * n1 + idx) * n2 + c; }
+    return e * n2 + idx;                                                  // dim == 2: stride n2
+}
+
+__global__ void pack_plane_kernel(const double* __restrict__ A, int n0, int n1, int n2, int dim, int idx,
+                                  double* __restrict__ buf, size_t count) {
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < count; e += (size_t)gridDim.x * blockDim.x)
+        buf[e] = A[plane_elem(n0, n1, n2, dim, idx, e)];
+}
+
+__global__ void unpack_plane_kernel(double* __restrict__ A, int n0, int n1, int n2, int dim, int idx,
+                                    const double* __restrict__ buf, size_t count) {
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < count; e += (size_t)gridDim.x * blockDim.x)
+        A[plane_elem(n0, n1, n2, dim, idx, e)] = buf[e];
+}
+
+__global__ void extract_inner_kernel(const double* __restrict__ A, int n0, int n1, int n2, int m0, int m1, int m2,
+                                     int o0, int o1, int o2, double* __restrict__ out) {
+    const size_t count = (size_t)m0 * m1 * m2;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < count; e += (size_t)gridDim.x * blockDim.x) {
+        const size_t c = e % m2, b = (e / m2) % m1, a = e / ((size_t)m1 * m2);
+        out[e] = A[((a + o0) * n1 + (b + o1)) * n2 + (c + o2)];
+    }
+}
+
+// ---- max / sum reduction ----------------------------------------------------------------------------
+// Two-level: every block writes its partial {max, sum} to scratch and takes a ticket; the block that
+// draws the last ticket folds the partials in a fixed order (deterministic result) and resets the
+// ticket for the next call.
+constexpr int RED_THREADS = 256;
+constexpr int RED_MAX_BLOCKS = 1024;
+
+struct RedScratch {
+    unsigned int ticket;
+    unsigned int pad[3];
+    double pmax[RED_MAX_BLOCKS];
+    double psum[RED_MAX_BLOCKS];
+};
+
+__device__ __forceinline__ void block_reduce(double& mx, double& sm, double* sh_max, double* sh_sum) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+        sm += __shfl_xor_sync(0xffffffffu, sm, off);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { sh_max[w] = mx; sh_sum[w] = sm; }
+    __syncthreads();
+    if (w == 0) {
+        mx = l < RED_THREADS / 32 ? sh_max[l] : -INFINITY;
+        sm = l < RED_THREADS / 32 ? sh_sum[l] : 0.0;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+            sm += __shfl_xor_sync(0xffffffffu, sm, off);
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(RED_THREADS) reduce_max_sum_kernel(const double* __restrict__ x, size_t n,
+                                                                     RedScratch* sc, double* __restrict__ out) {
+    __shared__ double sh_max[RED_THREADS / 32], sh_sum[RED_THREADS / 32];
+    __shared__ bool is_last;
+    double mx = -INFINITY, sm = 0.0;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+        const double v = x[e];
+        mx = fmax(mx, v);
+        sm += v;
+    }
+    block_reduce(mx, sm, sh_max, sh_sum);
+    if (threadIdx.x == 0) {
+        sc->pmax[blockIdx.x] = mx;
+        sc->psum[blockIdx.x] = sm;
+        __threadfence();
+        const unsigned int t = atomicAdd(&sc->ticket, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        mx = -INFINITY;
+        sm = 0.0;
+        for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x) {
+            mx = fmax(mx, sc->pmax[b]);
+            sm += sc->psum[b];
+        }
+        block_reduce(mx, sm, sh_max, sh_sum);
+        if (threadIdx.x == 0) {
+            out[0] = mx;
+            out[1] = sm;
+            sc->ticket = 0;   // ready for the next call on this scratch
+        }
+    }
+}
+
+// ---- colour map (reference scripts/diffusion_2D_ap.jl:47 heatmap rasterisation, K15) -----------------
+__global__ void colormap_kernel(const double* __restrict__ f, size_t n, double vmin, double scale,
+                                const uint8_t* __restrict__ lut, uint8_t* __restrict__ rgb) {
+    __shared__ uint8_t s_lut[768];
+    for (int k = threadIdx.x; k < 768; k += blockDim.x) s_lut[k] = lut[k];
+    __syncthreads();
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+        double t = floor((f[e] - vmin) * scale + 0.5);
+        t = t < 0.0 ? 0.0 : (t > 255.0 ? 255.0 : t);
+        const int k = (int)t * 3;
+        rgb[3 * e + 0] = s_lut[k + 0];
+        rgb[3 * e + 1] = s_lut[k + 1];
+        rgb[3 * e + 2] = s_lut[k + 2];
+    }
+}
+
+static int grid_for(size_t count, int threads, int cap_mult = 8) {
+    size_t b = (count + threads - 1) / threads;
+    const size_t cap = (size_t)igg::sm_count() * cap_mult;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+}  // namespace
+
+extern "C" {
+
+int igg_gaussian_ic2d(double* T, int nx, int ny, double x0, double y0, double dx, double dy, double lx, double ly,
+                      void* stream) {
+    IGG_REQUIRE(T && nx > 0 && ny > 0, "igg_gaussian_ic2d: bad arguments");
+    dim3 blk(32, 8), grd(igg::ceil_div(ny, 32), igg::ceil_div(nx, 8));
+    IGG_REQUIRE(grd.y <= 65535, "igg_gaussian_ic2d: nx too large for this launch shape");
+    gaussian_ic2d_kernel<<<grd, blk, 0, (cudaStream_t)stream>>>(T, nx, ny, x0, y0, dx, dy, lx, ly);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+int igg_gaussian_ic3d(double* T, int nx, int ny, int nz, double x0, double y0, double z0, double dx, double dy,
+                      double dz, double lx, double ly, double lz, void* stream) {
+    IGG_REQUIRE(T && nx > 0 && ny > 0 && nz > 0, "igg_gaussian_ic3d: bad arguments");
+    dim3 blk(32, 8), grd(igg::ceil_div(nz, 32), igg::ceil_div(ny, 8), nx);
+    IGG_REQUIRE(grd.y <= 65535 && grd.z <= 65535, "igg_gaussian_ic3d: grid too large");
+    gaussian_ic3d_kernel<<<grd, blk, 0, (cudaStream_t)stream>>>(T, nx, ny, nz, x0, y0, z0, dx, dy, dz, lx, ly, lz);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+int igg_pack_plane(const double* A, int n0, int n1, int n2, int dim, int idx, double* buf, void* stream) {
+    IGG_REQUIRE(A && buf && n0 > 0 && n1 > 0 && n2 > 0 && dim >= 0 && dim < 3, "igg_pack_plane: bad arguments");
+    const int nd[3] = {n0, n1, n2};
+    IGG_REQUIRE(idx >= 0 && idx < nd[dim], "igg_pack_plane: plane index out of range");
+    const size_t count = (size_t)n0 * n1 * n2 / nd[dim];
+    pack_plane_kernel<<<grid_for(count, 256), 256, 0, (cudaStream_t)stream>>>(A, n0, n1, n2, dim, idx, buf, count);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+int igg_unpack_plane(double* A, int n0, int n1, int n2, int dim, int idx, const double* buf, void* stream) {
+    IGG_REQUIRE(A && buf && n0 > 0 && n1 > 0 && n2 > 0 && dim >= 0 && dim < 3, "igg_unpack_plane: bad arguments");
+    const int nd[3] = {n0, n1, n2};
+    IGG_REQUIRE(idx >= 0 && idx < nd[dim], "igg_unpack_plane: plane index out of range");
+    const size_t count = (size_t)n0 * n1 * n2 / nd[dim];
+    unpack_plane_kernel<<<grid_for(count, 256), 256, 0, (cudaStream_t)stream>>>(A, n0, n1, n2, dim, idx, buf, count);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+int igg_extract_inner(const double* A, int n0, int n1, int n2, double* out, void* stream) {
+    IGG_REQUIRE(A && out && n0 > 0 && n1 > 0 && n2 > 0, "igg_extract_inner: bad arguments");
+    const int o0 = n0 > 2, o1 = n1 > 2, o2 = n2 > 2;
+    const int m0 = n0 - 2 * o0, m1 = n1 - 2 * o1, m2 = n2 - 2 * o2;
+    const size_t count = (size_t)m0 * m1 * m2;
+    extract_inner_kernel<<<grid_for(count, 256), 256, 0, (cudaStream_t)stream>>>(A, n0, n1, n2, m0, m1, m2, o0, o1,
+                                                                                o2, out);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+size_t igg_reduce_scratch_bytes(size_t n) {
+    (void)n;
+    return sizeof(RedScratch);
+}
+
+int igg_reduce_max_sum(const double* x, size_t n, void* scratch, double* out, void* stream) {
+    IGG_REQUIRE(x && scratch && out && n > 0, "igg_reduce_max_sum: bad arguments");
+    IGG_REQUIRE(((uintptr_t)scratch & 15) == 0, "igg_reduce_max_sum: scratch must be 16-byte aligned");
+    int blocks = grid_for(n, RED_THREADS, 4);
+    if (blocks > RED_MAX_BLOCKS) blocks = RED_MAX_BLOCKS;
+    reduce_max_sum_kernel<<<blocks, RED_THREADS, 0, (cudaStream_t)stream>>>(x, n, (RedScratch*)scratch, out);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+int igg_colormap(const double* field, size_t n, double vmin, double vmax, const uint8_t* lut_dev, uint8_t* rgb,
+                 void* stream) {
+    IGG_REQUIRE(field && lut_dev && rgb && n > 0, "igg_colormap: bad arguments");
+    const double scale = vmax > vmin ? 255.0 / (vmax - vmin) : 0.0;
+    colormap_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(field, n, vmin, scale, lut_dev, rgb);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

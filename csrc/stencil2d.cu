@@ -1,0 +1,355 @@
+// 2-D heat-diffusion step, fused form, for sm_100a.
+//
+// Provides the behaviour of the reference's fused kernel `diffusion_step!`
+// (scripts/diffusion_2D_perf.jl:3-13) and of its boundary/interior split
+// (scripts/diffusion_2D_perf_hide.jl:15-29, predicates :20-21), plus -- when a push descriptor is
+// given -- the halo exchange that the reference performs afterwards with update_halo!
+// (scripts/diffusion_2D_perf.jl:51).  The design is new:
+//
+//  * variant 1 (product): a persistent kernel, one CTA per SM.  Each CTA walks a static list of
+//    32x128-cell tiles; thread 0 keeps a 3-stage ring of TMA loads in flight (the T tile with its
+//    one-cell halo -- out-of-bounds zero fill handles array edges -- and the matching Cp tile), all
+//    threads consume a stage after its mbarrier flips, computing from shared memory with a 3-row
+//    register window and 16-byte loads, and write T2 with 16-byte streaming stores.
+//  * boundary-frame tiles come first in the list, so edge cells are pushed into the neighbours'
+//    halo cells (peer stores over NVLink) and their epoch flag is released while the bulk of the
+//    interior is still being computed: communication is hidden inside ONE launch.
+//  * variant 0: straightforward direct-load kernel with the same tiling, masks and push logic;
+//    it is the "recompiled baseline" flavour and the fallback for odd ny.
+//
+// Layout: T[ix][iy], iy contiguous.  "x" rows are strided, "y" columns contiguous.
+#include <string.h>
+
+#include "push.cuh"
+
+namespace {
+
+using namespace igg;
+
+constexpr int BX = 32;          // tile rows
+constexpr int BY = 128;         // tile columns (contiguous)
+constexpr int STAGES = 3;
+constexpr int TP = BY + 2;      // smem pitch of the T tile (doubles)
+constexpr int T_TILE_BYTES = (BX + 2) * TP * 8;                      // 35360
+constexpr int T_TILE_PAD = (T_TILE_BYTES + 127) / 128 * 128;         // 35456
+constexpr int CP_TILE_BYTES = BX * BY * 8;                           // 32768
+constexpr int STAGE_BYTES = T_TILE_PAD + CP_TILE_BYTES;              // 68224
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 64;                // + mbarriers
+
+struct Seg {
+    int i0, j0, w, h, start;    // tiles [i0,i0+h) x [j0,j0+w); `start` = linear id of its first tile
+};
+struct TileSet {
+    Seg s[5];
+    int nseg, ntiles;
+};
+
+struct Params {
+    const double* T;
+    double* T2;
+    const double* Cp;
+    int nx, ny;
+    double lam, dt, _dx, _dy;
+    const double* dev_params;   // optional {lam, dt, _dx, _dy} in device memory
+    int mode, bwx, bwy;
+    int i_hi, j_hi;             // tile row/column that contains x==nx-2 / y==ny-2
+    TileSet ts;
+    int has_push;
+    int edge_tiles[9];
+    igg_push2d push;
+};
+
+__device__ __forceinline__ void tile_of(const TileSet& ts, int t, int& i, int& j) {
+    i = 0;
+    j = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        if (k < ts.nseg) {
+            const Seg& s = ts.s[k];
+            const int r = t - s.start;
+            if (r >= 0 && r < s.w * s.h) {
+                i = s.i0 + r / s.w;
+                j = s.j0 + r % s.w;
+            }
+        }
+    }
+}
+
+// The arithmetic of reference scripts/diffusion_2D_perf.jl:8-10, operation for operation.
+__device__ __forceinline__ double update_cell(double c, double xm, double xp, double ym, double yp, double cp,
+                                              double lam, double dt, double _dx, double _dy) {
+    const double qxr = -lam * (xp - c) * _dx;
+    const double qxl = -lam * (c - xm) * _dx;
+    const double qyt = -lam * (yp - c) * _dy;
+    const double qyb = -lam * (c - ym) * _dy;
+    return c + dt * (cp * (-(qxr - qxl) * _dx - (qyt - qyb) * _dy));
+}
+
+// is (x,y) computed in this mode?  (interior test done by the caller)
+__device__ __forceinline__ bool in_frame(const Params& p, int x, int y) {
+    return x <= p.bwx || x >= p.nx - 1 - p.bwx || y <= p.bwy || y >= p.ny - 1 - p.bwy;
+}
+
+// ------------------------------------------------------------------------------------------------
+// variant 1: persistent, TMA + mbarrier pipeline
+// ------------------------------------------------------------------------------------------------
+template <int RPT>   // rows per thread
+__global__ void __launch_bounds__((BY / 2) * (BX / RPT), 1)
+diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapCp,
+                  const __grid_constant__ Params p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    const int tid = threadIdx.x;
+    const int ntiles = p.ts.ntiles;
+    const int first = blockIdx.x;
+    const int n_my = first < ntiles ? (ntiles - first + gridDim.x - 1) / gridDim.x : 0;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        fence_mbar_init();
+        tma_prefetch_desc(&mapT);
+        tma_prefetch_desc(&mapCp);
+    }
+    __syncthreads();
+
+    auto issue = [&](int k) {
+        int i, j;
+        tile_of(p.ts, first + k * gridDim.x, i, j);
+        if (p.has_push) {
+            wait_faces_2d(p.push, i == 0, i == p.i_hi, j == 0, j == p.j_hi);
+            fence_proxy_async();
+        }
+        const int s = k % STAGES;
+        unsigned char* st = smem + s * STAGE_BYTES;
+        mbar_arrive_expect_tx(&full[s], T_TILE_BYTES + CP_TILE_BYTES);
+        tma_load_2d(st, &mapT, &full[s], j * BY - 1, i * BX - 1);
+        tma_load_2d(st + T_TILE_PAD, &mapCp, &full[s], j * BY, i * BX);
+    };
+
+    if (tid == 0) {
+        for (int k = 0; k < STAGES - 1 && k < n_my; ++k) issue(k);
+    }
+
+    const int cp = tid % (BY / 2);   // column pair
+    const int rg = tid / (BY / 2);   // row group
+    const double lam = p.dev_params ? p.dev_params[0] : p.lam, dt = p.dev_params ? p.dev_params[1] : p.dt;
+    const double _dx = p.dev_params ? p.dev_params[2] : p._dx, _dy = p.dev_params ? p.dev_params[3] : p._dy;
+
+    for (int k = 0; k < n_my; ++k) {
+        if (tid == 0 && k + STAGES - 1 < n_my) issue(k + STAGES - 1);
+        int i, j;
+        tile_of(p.ts, first + k * gridDim.x, i, j);
+        const int s = k % STAGES;
+        mbar_wait(&full[s], (k / STAGES) & 1);
+
+        const double* sT = reinterpret_cast<const double*>(smem + s * STAGE_BYTES) + (rg * RPT) * TP + 2 * cp;
+        const double* sC = reinterpret_cast<const double*>(smem + s * STAGE_BYTES + T_TILE_PAD) +
+                           (rg * RPT) * BY + 2 * cp;
+        const int y = j * BY + 2 * cp;
+        const int xb = i * BX + rg * RPT;
+        const bool edge_tile = p.has_push && (i == 0 || i == p.i_hi || j == 0 || j == p.j_hi);
+        // column validity is fixed per thread
+        const bool vy0 = (y >= 1) && (y <= p.ny - 2);
+        const bool vy1 = (y + 1 <= p.ny - 2);
+
+        double2 a0 = *reinterpret_cast<const double2*>(sT);
+        double2 a1 = *reinterpret_cast<const double2*>(sT + 2);
+        double2 b0 = *reinterpret_cast<const double2*>(sT + TP);
+        double2 b1 = *reinterpret_cast<const double2*>(sT + TP + 2);
+#pragma unroll
+        for (int r = 0; r < RPT; ++r) {
+            const double2 c0 = *reinterpret_cast<const double2*>(sT + (r + 2) * TP);
+            const double2 c1 = *reinterpret_cast<const double2*>(sT + (r + 2) * TP + 2);
+            const double2 cc = *reinterpret_cast<const double2*>(sC + r * BY);
+            const int x = xb + r;
+            const double vA = update_cell(b0.y, a0.y, c0.y, b0.x, b1.x, cc.x, lam, dt, _dx, _dy);
+            const double vB = update_cell(b1.x, a1.x, c1.x, b0.y, b1.y, cc.y, lam, dt, _dx, _dy);
+            const bool vx = (x >= 1) && (x <= p.nx - 2);
+            bool wA = vx && vy0, wB = vx && vy1;
+            if (p.mode != 0) {
+                const bool fA = in_frame(p, x, y), fB = in_frame(p, x, y + 1);
+                wA = wA && (p.mode == 1 ? fA : !fA);
+                wB = wB && (p.mode == 1 ? fB : !fB);
+            }
+            double* out = p.T2 + (size_t)x * p.ny + y;
+            if (wA && wB) {
+                st_cs_f64x2(out, vA, vB);
+            } else {
+                if (wA) st_cs_f64(out, vA);
+                if (wB) st_cs_f64(out + 1, vB);
+            }
+            if (edge_tile) {
+                if (wA) push_cell_2d(p.push, p.nx, p.ny, x, y, vA);
+                if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
+            }
+            a0 = b0; a1 = b1; b0 = c0; b1 = c1;
+        }
+        __syncthreads();   // stage s may be refilled; all remote stores of this tile were issued
+        if (edge_tile && tid == 0)
+            signal_edges_2d(p.push, p.edge_tiles, i == 0, i == p.i_hi, j == 0, j == p.j_hi);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// variant 0: direct global loads, one CTA per tile, one cell per thread per row
+// ------------------------------------------------------------------------------------------------
+constexpr int DBX = 16;
+__global__ void __launch_bounds__(256) diff2d_direct_kernel(const __grid_constant__ Params p) {
+    int i, j;
+    tile_of(p.ts, blockIdx.x, i, j);
+    // here tiles are BX x BY as well; 256 threads = 2 row groups x 128 columns, 16 rows each
+    const int tid = threadIdx.x;
+    const int y = j * BY + (tid % BY);
+    const int xb = i * BX + (tid / BY) * DBX;
+    const bool edge_tile = p.has_push && (i == 0 || i == p.i_hi || j == 0 || j == p.j_hi);
+    if (p.has_push) {
+        if (tid == 0) wait_faces_2d(p.push, i == 0, i == p.i_hi, j == 0, j == p.j_hi);
+        __syncthreads();
+    }
+    const bool vy = (y >= 1) && (y <= p.ny - 2);
+    const double lam = p.dev_params ? p.dev_params[0] : p.lam, dt = p.dev_params ? p.dev_params[1] : p.dt;
+    const double _dx = p.dev_params ? p.dev_params[2] : p._dx, _dy = p.dev_params ? p.dev_params[3] : p._dy;
+    if (vy) {
+        const int nx = p.nx, ny = p.ny;
+        int x = xb < 1 ? 1 : xb;
+        const int xe = min(xb + DBX, nx - 1);
+        if (x < xe) {
+            const double* Tc = p.T + (size_t)x * ny + y;
+            double up = Tc[-ny], c = Tc[0];
+            for (; x < xe; ++x) {
+                const double dn = Tc[ny];
+                const double v = update_cell(c, up, dn, Tc[-1], Tc[1], p.Cp[(size_t)x * ny + y], lam, dt, _dx,
+                                             _dy);
+                bool w = true;
+                if (p.mode != 0) {
+                    const bool f = in_frame(p, x, y);
+                    w = (p.mode == 1) ? f : !f;
+                }
+                if (w) {
+                    p.T2[(size_t)x * ny + y] = v;
+                    if (edge_tile) push_cell_2d(p.push, nx, ny, x, y, v);
+                }
+                up = c;
+                c = dn;
+                Tc += ny;
+            }
+        }
+    }
+    if (edge_tile) {
+        __syncthreads();
+        if (tid == 0) signal_edges_2d(p.push, p.edge_tiles, i == 0, i == p.i_hi, j == 0, j == p.j_hi);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host: tile lists
+// ------------------------------------------------------------------------------------------------
+static void add_seg(TileSet& ts, int i0, int i1, int j0, int j1) {   // inclusive tile ranges
+    if (i1 < i0 || j1 < j0) return;
+    Seg& s = ts.s[ts.nseg++];
+    s.i0 = i0;
+    s.j0 = j0;
+    s.h = i1 - i0 + 1;
+    s.w = j1 - j0 + 1;
+    s.start = ts.ntiles;
+    ts.ntiles += s.w * s.h;
+}
+
+static void build_tiles(TileSet& ts, int nx, int ny, int mode, int bwx, int bwy) {
+    ts.nseg = 0;
+    ts.ntiles = 0;
+    const int nti = (nx - 2) / BX + 1, ntj = (ny - 2) / BY + 1;
+    if (mode == 2) {
+        const int x0 = 1 + bwx, x1 = nx - 2 - bwx, y0 = 1 + bwy, y1 = ny - 2 - bwy;
+        if (x1 < x0 || y1 < y0) return;
+        add_seg(ts, x0 / BX, x1 / BX, y0 / BY, y1 / BY);
+        return;
+    }
+    // tile rows / columns that intersect the boundary frame
+    int a0 = (bwx < nx - 2 ? bwx : nx - 2) / BX;                 // last row of the low band
+    int a1 = (nx - 1 - bwx > 1 ? nx - 1 - bwx : 1) / BX;         // first row of the high band
+    int b0 = (bwy < ny - 2 ? bwy : ny - 2) / BY;
+    int b1 = (ny - 1 - bwy > 1 ? ny - 1 - bwy : 1) / BY;
+    if (a1 <= a0) {  // bands meet: everything is frame
+        add_seg(ts, 0, nti - 1, 0, ntj - 1);
+        return;
+    }
+    add_seg(ts, 0, a0, 0, ntj - 1);
+    add_seg(ts, a1, nti - 1, 0, ntj - 1);
+    if (b1 <= b0) {
+        add_seg(ts, a0 + 1, a1 - 1, 0, ntj - 1);
+        return;
+    }
+    add_seg(ts, a0 + 1, a1 - 1, 0, b0);
+    add_seg(ts, a0 + 1, a1 - 1, b1, ntj - 1);
+    if (mode == 0) add_seg(ts, a0 + 1, a1 - 1, b0 + 1, b1 - 1);
+}
+
+static bool g_attr_set[64] = {false};   // per device: opt-in dynamic shared memory size applied
+
+}  // namespace
+
+extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
+                                    double dt, double _dx, double _dy, const double* dev_params, int mode, int bwx,
+                                    int bwy, int variant, const igg_push2d* push, void* stream) {
+    IGG_REQUIRE(T && T2 && Cp, "igg_diffusion2d_step: null field pointer");
+    IGG_REQUIRE(nx >= 3 && ny >= 3, "igg_diffusion2d_step: need nx, ny >= 3 (got %d x %d)", nx, ny);
+    IGG_REQUIRE(mode >= 0 && mode <= 2, "igg_diffusion2d_step: mode must be 0, 1 or 2");
+    IGG_REQUIRE(variant == 0 || variant == 1, "igg_diffusion2d_step: variant must be 0 or 1");
+    IGG_REQUIRE(mode == 0 || (bwx >= 1 && bwy >= 1), "igg_diffusion2d_step: b_width must be >= 1 in split modes");
+    IGG_REQUIRE(!(push && mode == 2), "igg_diffusion2d_step: the interior pass (mode 2) never pushes");
+    if (bwx < 1) bwx = 1;
+    if (bwy < 1) bwy = 1;
+    Params p;
+    p.T = T; p.T2 = T2; p.Cp = Cp; p.nx = nx; p.ny = ny;
+    p.lam = lam; p.dt = dt; p._dx = _dx; p._dy = _dy;
+    p.dev_params = dev_params;
+    p.mode = mode; p.bwx = bwx; p.bwy = bwy;
+    p.i_hi = (nx - 2) / BX;
+    p.j_hi = (ny - 2) / BY;
+    build_tiles(p.ts, nx, ny, mode, bwx, bwy);
+    if (p.ts.ntiles == 0) return 0;
+    p.has_push = push ? 1 : 0;
+    const int nti = p.i_hi + 1, ntj = p.j_hi + 1;
+    for (int sx = -1; sx <= 1; ++sx)
+        for (int sy = -1; sy <= 1; ++sy)
+            p.edge_tiles[(sx + 1) * 3 + (sy + 1)] = (sx != 0 && sy != 0) ? 1 : (sx != 0 ? ntj : nti);
+    if (push) {
+        p.push = *push;
+        IGG_REQUIRE(push->epoch >= 1, "igg_diffusion2d_step: push epoch must be >= 1");
+    } else {
+        memset(&p.push, 0, sizeof(p.push));
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (variant == 1) {
+        if ((ny & 1) || (((uintptr_t)T | (uintptr_t)T2 | (uintptr_t)Cp) & 15)) {
+            igg::set_error("igg_diffusion2d_step: the TMA variant needs even ny and 16-byte aligned fields "
+                           "(ny=%d); use variant 0", ny);
+            return IGG_ERR_UNSUPPORTED;
+        }
+        CUtensorMap mT, mC;
+        const uint64_t dims[2] = {(uint64_t)ny, (uint64_t)nx};
+        const uint32_t boxT[2] = {BY + 2, BX + 2};
+        const uint32_t boxC[2] = {BY, BX};
+        int rc = igg::get_tensor_map_f64(T, 2, dims, boxT, &mT);
+        if (rc) return rc;
+        rc = igg::get_tensor_map_f64(Cp, 2, dims, boxC, &mC);
+        if (rc) return rc;
+        constexpr int RPT = 4;
+        auto kern = diff2d_tma_kernel<RPT>;
+        int dev = 0;
+        IGG_CUDA_OK(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !g_attr_set[dev]) {
+            IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+            if (dev >= 0 && dev < 64) g_attr_set[dev] = true;
+        }
+        const int grid = p.ts.ntiles < igg::sm_count() ? p.ts.ntiles : igg::sm_count();
+        kern<<<grid, (BY / 2) * (BX / RPT), SMEM_BYTES, st>>>(mT, mC, p);
+        IGG_LAUNCH_CHECK();
+    } else {
+        diff2d_direct_kernel<<<p.ts.ntiles, 256, 0, st>>>(p);
+        IGG_LAUNCH_CHECK();
+    }
+    return 0;
+}

@@ -1,0 +1,179 @@
+/* igg_b200.h -- C ABI of the native library (libigg_b200.so), sm_100a only.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a positive cudaError_t value when a CUDA call failed,
+ *     or a negative IGG_ERR_* code; igg_last_error() then holds a readable message (per thread);
+ *   - `stream` is a cudaStream_t passed as void* (0 = default stream); all work is asynchronous
+ *     with respect to the host unless stated otherwise;
+ *   - fields are row-major fp64 arrays T[ix][iy]([iz]) with the LAST index contiguous; sizes are the
+ *     local sizes including the one-cell halo; indices are 0-based.
+ *
+ * The reference (williamfgc/ROCm-MPI) contains no native code; each declaration cites the
+ * reference lines whose behaviour it provides.
+ */
+#ifndef IGG_B200_H
+#define IGG_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IGG_ERR_INVALID (-1)      /* bad argument                                   */
+#define IGG_ERR_UNSUPPORTED (-2)  /* shape/alignment not supported by this variant  */
+#define IGG_ERR_TIMEOUT (-3)      /* a cross-GPU flag wait gave up                  */
+
+#define IGG_MAX_NEIGHBORS 27      /* 3x3x3 offsets, centre unused                   */
+#define IGG_FLAG_BANKS 32         /* independent flag channels per rank             */
+#define IGG_FLAG_BANK_STRIDE 64   /* uint64 slots per bank                          */
+
+/* ---- library / device ---------------------------------------------------------------------- */
+int igg_version(void);
+const char* igg_last_error(void);
+int igg_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin_bytes);
+/* number of kernels this library has launched in this process (bench.py's "gpu_launches") */
+unsigned long long igg_launch_count(void);
+
+/* ---- 2-D diffusion, fused form (reference scripts/diffusion_2D_perf.jl:3-13,
+ *      split form scripts/diffusion_2D_perf_hide.jl:15-29) -------------------------------------
+ * T2[ix][iy] = T + dt*(Cp*(-(qxR-qxL)*_dx - (qyT-qyB)*_dy)) on the interior; boundary cells of T2
+ * are never written.
+ *   mode 0: whole interior (boundary-frame tiles are scheduled first);
+ *   mode 1: only the frame of width (bwx,bwy) -- istep==1 of the reference split kernel;
+ *   mode 2: only the cells inside the frame  -- istep==2.
+ *   variant 0: direct global loads ("recompiled baseline" flavour);
+ *   variant 1: persistent kernel, TMA-staged tiles + mbarrier pipeline (needs ny % 2 == 0).
+ * `push` may be NULL (no communication).  With a push descriptor the kernel also stores every
+ * freshly computed edge cell into the neighbours' halo cells over peer memory and signals them;
+ * tiles that read a halo plane first wait for that neighbour's signal of the previous epoch.
+ */
+typedef struct igg_push2d {
+    /* indexed [(ox+1)*3 + (oy+1)]: neighbour at Cartesian offset (ox,oy); NULL = no neighbour */
+    double* peer_dst[9];            /* base of the neighbour's destination array (same shape)   */
+    uint64_t* peer_flag[9];         /* slot in the NEIGHBOUR's flag pad that this rank signals   */
+    uint64_t* my_flag[9];           /* slot in MY flag pad that the neighbour at (ox,oy) signals */
+    uint64_t* my_count[9];          /* local tile-arrival counters (monotonic)                   */
+    uint64_t* err_word;             /* set (bit 63) if a wait timed out                          */
+    uint64_t epoch;                 /* this step's epoch; halo reads wait for epoch-1            */
+} igg_push2d;
+
+/* `dev_params` (may be NULL): device array {lam, dt, _dx, _dy} that overrides the by-value scalars,
+ * so a host control loop can feed per-step parameters through an asynchronous H2D copy. */
+int igg_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
+                         double dt, double _dx, double _dy, const double* dev_params, int mode, int bwx,
+                         int bwy, int variant, const igg_push2d* push, void* stream);
+
+/* ---- 2-D diffusion, three-kernel form (reference scripts/diffusion_2D_kp.jl:16-54) ------------ */
+int igg_flux2d(double* qx, double* qy, const double* T, int nx, int ny, double lam, double _dx,
+               double _dy, void* stream);
+int igg_residual2d(double* dTdt, const double* qx, const double* qy, const double* Cp, int nx, int ny,
+                   double _dx, double _dy, void* stream);
+/* Update! fused with the edge push (push may be NULL): T[inner] += dt*dTdt */
+int igg_update2d(double* T, const double* dTdt, int nx, int ny, double dt, const igg_push2d* push,
+                 void* stream);
+
+/* ---- 3-D diffusion (7-point; IGG capability, the reference itself is 2-D only) ---------------- */
+typedef struct igg_push3d {
+    double* peer_dst[27];
+    uint64_t* peer_flag[27];
+    uint64_t* my_flag[27];
+    uint64_t* my_count[27];
+    uint64_t* err_word;
+    uint64_t epoch;
+} igg_push3d;
+int igg_diffusion3d_step(const double* T, double* T2, const double* Cp, int nx, int ny, int nz,
+                         double lam, double dt, double _dx, double _dy, double _dz, int mode, int bwx,
+                         int bwy, int bwz, int variant, const igg_push3d* push, void* stream);
+
+/* ---- initial condition (reference scripts/diffusion_2D_ap.jl:28) ------------------------------- */
+int igg_gaussian_ic2d(double* T, int nx, int ny, double x0, double y0, double dx, double dy, double lx,
+                      double ly, void* stream);
+int igg_gaussian_ic3d(double* T, int nx, int ny, int nz, double x0, double y0, double z0, double dx,
+                      double dy, double dz, double lx, double ly, double lz, void* stream);
+
+/* ---- halo planes: pack / unpack (what IGG does inside update_halo!) ------------- */
+/* A has shape (n0,n1,n2) (use 1 for unused trailing dims); plane `idx` of dimension `dim`. */
+int igg_pack_plane(const double* A, int n0, int n1, int n2, int dim, int idx, double* buf, void* stream);
+int igg_unpack_plane(double* A, int n0, int n1, int n2, int dim, int idx, const double* buf, void* stream);
+/* interior extraction A[1:-1,...] -> dense buffer (reference scripts/diffusion_2D_ap.jl:45) */
+int igg_extract_inner(const double* A, int n0, int n1, int n2, double* out, void* stream);
+
+/* ---- peer-memory fabric (replaces GPU-aware MPI, reference scripts/rocmaware_test_selectdevice.jl:15-22)
+ * Allocations are plain cudaMalloc blocks that can be exported with CUDA IPC and mapped by the
+ * other ranks of the node. */
+int igg_fabric_alloc(size_t bytes, void** ptr);            /* zero-initialised, 512-byte aligned   */
+int igg_fabric_free(void* ptr);
+int igg_ipc_export(const void* ptr, void* handle64, uint64_t* offset); /* 64-byte handle + offset   */
+int igg_ipc_open(const void* handle64, void** base);       /* maps a peer allocation               */
+int igg_ipc_close(void* base);
+int igg_can_access_peer(int dev, int peer_dev, int* can);
+
+/* Flag pad layout.  Every rank owns a pad of IGG_FLAG_BANKS banks x IGG_FLAG_BANK_STRIDE uint64
+ * slots in fabric memory (peers signal into it) and a same-sized private pad of counters.
+ * Within a bank, slots are indexed by the neighbour offset o = ((ox+1)*3+(oy+1))*3+(oz+1) (2-D code
+ * uses oz = 0):
+ *   [IGG_SLOT_DATA  + o]  epoch of the last completed push FROM the neighbour at offset o
+ *   [IGG_SLOT_READY + o]  epoch up to which the neighbour at offset o is ready to RECEIVE
+ *   [IGG_SLOT_ERR]        error word (bit 63 set = a wait timed out)                                  */
+#define IGG_SLOT_DATA 0
+#define IGG_SLOT_READY 27
+#define IGG_SLOT_ERR 54
+#define IGG_SLOT_CTA_COUNT 55     /* counter pad only: CTA arrival counter of igg_halo_exchange_peer */
+
+/* update_halo over peer memory in ONE launch.  The dimension-sequential exchange of
+ * ImplicitGlobalGrid (x, then y, then z, each with full-extent planes) is
+ * algebraically a set of independent box copies to the up-to-26 neighbours, every box taken
+ * from cells that the exchange itself never writes; so the kernel does: ready handshake ->
+ * all boxes stored into the neighbours' arrays -> release the epoch -> wait for the neighbours'.
+ * `xfers` lives in device memory. */
+typedef struct igg_halo_xfer {
+    const double* src;              /* my array                                                   */
+    double* dst;                    /* the neighbour's array (peer-mapped; same shape)            */
+    int n[3];                       /* array shape (1 for unused trailing dims)                   */
+    int src_start[3];
+    int dst_start[3];
+    int extent[3];
+} igg_halo_xfer;
+typedef struct igg_halo_sync {
+    uint64_t* peer_bank[27];        /* flag bank base in the pad of the neighbour at offset o (NULL = none) */
+    uint64_t* my_bank;              /* my flag bank base                                           */
+    uint64_t* my_count_bank;        /* my counter bank base                                        */
+    uint64_t epoch;
+} igg_halo_sync;
+int igg_halo_exchange_peer(const igg_halo_xfer* xfers_dev, int nxfers, const igg_halo_sync* sync, void* stream);
+
+/* neighbour barrier on a bank: signal `epoch` into DATA slots of every neighbour, wait for theirs */
+int igg_neighbor_barrier(const igg_halo_sync* sync, void* stream);
+/* wait until the DATA slot of every neighbour in `sync` is >= sync->epoch (all pushes of that epoch
+ * have landed in my halo cells) */
+int igg_wait_epoch(const igg_halo_sync* sync, void* stream);
+/* peer-store copy kernel used by the ring test / bandwidth sweep: dst (peer) <- src (local), then
+ * *peer_flag = flag_value (release, system scope).  `my_count` is a private zero-initialised counter. */
+int igg_peer_copy(void* dst, const void* src, size_t bytes, uint64_t* peer_flag, uint64_t flag_value,
+                  uint64_t* my_count, void* stream);
+/* wait until *my_flag >= value */
+int igg_wait_value(uint64_t* my_flag, uint64_t value, uint64_t* err_word, void* stream);
+
+/* ---- diagnostics / output ---------------------------------------------------------------------- */
+/* max and sum of n fp64 values (reference scripts/diffusion_2D_perf_hide.jl:115 `@show maximum(T_v)`).
+ * `scratch`: igg_reduce_scratch_bytes(n) bytes of device memory, 16-byte aligned, zero-filled once
+ * before its first use (the kernel leaves it ready for the next call); calls sharing one scratch
+ * must not overlap on the GPU.  `out`: two device doubles {max, sum}. */
+size_t igg_reduce_scratch_bytes(size_t n);
+int igg_reduce_max_sum(const double* x, size_t n, void* scratch, double* out, void* stream);
+/* field -> RGB8 through a 256x3 look-up table (reference scripts/diffusion_2D_ap.jl:47 heatmap) */
+int igg_colormap(const double* field, size_t n, double vmin, double vmax, const uint8_t* lut_dev,
+                 uint8_t* rgb, void* stream);
+
+/* ---- CPU restatement (oracle + timed CPU baseline; the reference has no CPU path) --------------- */
+int igg_cpu_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
+                             double dt, double _dx, double _dy);
+int igg_cpu_diffusion2d_run(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
+                            double _dx, double _dy, int nt);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IGG_B200_H */

@@ -1,0 +1,186 @@
+"""``Diffusion2D``: the user-facing time stepper behind the perf / perf_hide applications.
+
+One object owns the fields (``T``, ``T2``, ``Cp``), the communication plan and the streams, and
+offers three ways to advance, all producing the same field:
+
+``fused``  ONE kernel per step: boundary-frame tiles first, their edge cells stored straight into
+           the neighbours' halo cells (NVLink peer stores) and the epoch flag released, while the
+           same launch goes on to compute the interior.  No pack, no library call, no unpack.
+``hide``   the reference's intended ``hide_communication`` structure
+           (``scripts/diffusion_2D_perf_hide.jl:94-101``): boundary frame of width ``b_width`` on a
+           high-priority stream (pushing edges as it goes), interior on a low-priority stream,
+           join, swap.
+``plain``  the reference's serial structure (``scripts/diffusion_2D_perf.jl:49-51``): full kernel,
+           swap, ``update_halo(T)`` over the chosen transport (``nccl`` = the same-box baseline).
+
+``step_controlled`` is the end-to-end form used by ``bench.py``: per step the host hands the step
+parameters over in pinned memory (asynchronous H2D copy, read by the kernel from device memory) and
+reads back the step's diagnostic ``[max(T), sum(T)]`` (D2H into pinned memory).
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from ..ops import native
+from ..ops import reference as ref
+from ..parallel import coords_g, global_grid, nx_g, ny_g, update_halo
+from ..parallel.fabric import PushPlan, fabric_zeros
+from ..parallel.halo import default_transport
+
+__all__ = ["Diffusion2D"]
+
+
+class Diffusion2D:
+    def __init__(self, nx: int, ny: int, *, lx: float = 10.0, ly: float = 10.0, lam: float = 1.0, Cp0: float = 1.0,
+                 mode: str = "fused", variant: str = "tma", b_width: Sequence[int] = (16, 4),
+                 transport: Optional[str] = None, host_ic: bool = False) -> None:
+        g = global_grid()
+        if g.device_type != "cuda":
+            raise RuntimeError("Diffusion2D runs on CUDA devices; use models.diffusion2d_ap on CPU")
+        if (nx, ny) != tuple(g.nxyz[:2]):
+            raise ValueError("nx, ny must be the local sizes given to init_global_grid")
+        if mode not in ("fused", "hide", "plain"):
+            raise ValueError("mode must be fused | hide | plain")
+        native.require()
+        self.g = g
+        self.nx, self.ny = nx, ny
+        self.lx, self.ly, self.lam, self.Cp0 = lx, ly, lam, Cp0
+        self.dx, self.dy = lx / nx_g(), ly / ny_g()
+        self._dx, self._dy = 1.0 / self.dx, 1.0 / self.dy
+        self.dt = ref.time_step(self.dx, self.dy, Cp0, lam)
+        self.mode, self.variant = mode, variant
+        self.b_width = (int(b_width[0]), int(b_width[1]))
+        dev = g.device
+        self.transport = transport or default_transport(torch.empty(0, device=dev))
+        self.uses_peer = mode in ("fused", "hide") or self.transport == "peer"
+        if variant == "tma" and ny % 2:
+            raise ValueError("variant 'tma' needs an even ny (16-byte row pitch); use variant='direct'")
+        # fields: peer-addressable when any peer path is in use
+        if self.uses_peer:
+            self.T = fabric_zeros((nx, ny))
+            self.T2 = fabric_zeros((nx, ny))
+        else:
+            self.T = torch.zeros(nx, ny, dtype=torch.float64, device=dev)
+            self.T2 = torch.zeros(nx, ny, dtype=torch.float64, device=dev)
+        self.Cp = torch.full((nx, ny), float(Cp0), dtype=torch.float64, device=dev)
+        self._init_condition(host_ic)
+        self.T2.copy_(self.T)                      # reference scripts/diffusion_2D_perf.jl:36
+        self.plan: Optional[PushPlan] = None
+        if mode in ("fused", "hide"):
+            self.plan = PushPlan(self.T, self.T2)
+        self._running = False
+        self.steps_done = 0
+        # streams for the hide structure (reference perf_hide.jl:63-68: HIGH / LOW priority queues)
+        self._s_hi = self._s_lo = None
+        if mode == "hide":
+            lo_p, hi_p = -1, 0
+            try:
+                lo_p, hi_p = torch.cuda.Stream.priority_range()
+            except Exception:
+                pass
+            self._s_hi = torch.cuda.Stream(device=dev, priority=-1)
+            self._s_lo = torch.cuda.Stream(device=dev, priority=0)
+            self._ev_hi = torch.cuda.Event()
+            self._ev_lo = torch.cuda.Event()
+            self._ev_main = torch.cuda.Event()
+        # end-to-end control path
+        self._params_dev = torch.zeros(4, dtype=torch.float64, device=dev)
+        self._params_pin = torch.zeros(4, dtype=torch.float64).pin_memory()
+        self._diag_dev = torch.zeros(2, dtype=torch.float64, device=dev)
+        self._diag_pin = torch.zeros(2, dtype=torch.float64).pin_memory()
+
+    # -- set-up -----------------------------------------------------------------------------------
+    def _init_condition(self, host_ic: bool) -> None:
+        g = self.g
+        probe = torch.empty((self.nx, self.ny), device="meta")
+        if host_ic or g.periods[0] or g.periods[1]:
+            # the reference's way: host comprehension, then upload (scripts/diffusion_2D_ap.jl:28)
+            xs = coords_g(0, self.dx, probe)
+            ys = coords_g(1, self.dy, probe)
+            self.T.copy_(ref.gaussian_ic(xs, ys, self.dx, self.dy, self.lx, self.ly))
+        else:
+            x0 = float(coords_g(0, self.dx, probe)[0])
+            y0 = float(coords_g(1, self.dy, probe)[0])
+            native.gaussian_ic_2d(self.T, x0, y0, self.dx, self.dy, self.lx, self.ly)
+
+    def begin(self) -> None:
+        """Collective: make halos consistent and open the push epoch sequence."""
+        if self.plan is not None:
+            self.plan.begin()
+        elif self.g.nprocs > 1 or any(self.g.periods):
+            update_halo(self.T, self.T2, transport=self.transport)
+        self._running = True
+
+    def finish(self) -> None:
+        """Collective: all pushes have landed; after this the halos of ``T`` are valid."""
+        if self._s_hi is not None:
+            torch.cuda.current_stream().wait_stream(self._s_hi)
+            torch.cuda.current_stream().wait_stream(self._s_lo)
+        if self.plan is not None and self._running:
+            self.plan.finish()
+        self._running = False
+
+    # -- stepping ---------------------------------------------------------------------------------
+    def _kernel(self, mode: int, push, dev_params=None) -> None:
+        native.diffusion2d_step(self.T2, self.T, self.Cp, self.lam, self.dt, self._dx, self._dy, mode=mode,
+                                b_width=self.b_width, variant=self.variant, push=push, dev_params=dev_params)
+
+    def step(self, n: int = 1, dev_params: Optional[torch.Tensor] = None) -> None:
+        if not self._running:
+            self.begin()
+        for _ in range(n):
+            if self.mode == "fused":
+                self._kernel(0, self.plan.next(self.T2), dev_params)
+                self.T, self.T2 = self.T2, self.T
+            elif self.mode == "hide":
+                main = torch.cuda.current_stream()
+                self._ev_main.record(main)
+                self._s_hi.wait_event(self._ev_main)
+                self._s_lo.wait_event(self._ev_main)
+                with torch.cuda.stream(self._s_hi):
+                    self._kernel(1, self.plan.next(self.T2), dev_params)     # frame + push
+                    self._ev_hi.record(self._s_hi)
+                with torch.cuda.stream(self._s_lo):
+                    self._kernel(2, None, dev_params)                       # interior
+                    self._ev_lo.record(self._s_lo)
+                main.wait_event(self._ev_hi)
+                main.wait_event(self._ev_lo)
+                self.T, self.T2 = self.T2, self.T
+            else:
+                self._kernel(0, None, dev_params)
+                self.T, self.T2 = self.T2, self.T
+                if self.g.nprocs > 1 or any(self.g.periods):
+                    update_halo(self.T, transport=self.transport)
+            self.steps_done += 1
+
+    def step_controlled(self, lam: Optional[float] = None, dt: Optional[float] = None) -> Tuple[float, float]:
+        """One end-to-end step: parameters in through pinned memory, ``(max, sum)`` of the new field out."""
+        p = self._params_pin
+        p[0] = self.lam if lam is None else lam
+        p[1] = self.dt if dt is None else dt
+        p[2] = self._dx
+        p[3] = self._dy
+        self._params_dev.copy_(p, non_blocking=True)                   # H2D, 32 bytes
+        self.step(1, dev_params=self._params_dev)
+        native.reduce_max_sum(self.T.view(-1), self._diag_dev)
+        self._diag_pin.copy_(self._diag_dev, non_blocking=True)        # D2H, 16 bytes
+        torch.cuda.current_stream().synchronize()
+        return float(self._diag_pin[0]), float(self._diag_pin[1])
+
+    h2d_bytes_per_step = 32
+    d2h_bytes_per_step = 16
+
+    def kernels_per_step(self) -> int:
+        """Native kernel launches per ``step()`` (for launch accounting)."""
+        if self.mode == "fused":
+            return 1
+        if self.mode == "hide":
+            return 2
+        return 1
+
+    def max_sum(self) -> Tuple[float, float]:
+        out = native.reduce_max_sum(self.T.view(-1))
+        v = out.cpu()
+        return float(v[0]), float(v[1])

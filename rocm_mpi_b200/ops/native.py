@@ -1,9 +1,288 @@
 """ctypes bindings to the in-tree native library ``rocm_mpi_b200/_lib/libigg_b200.so``.
 
-Filled in below; ``available()`` is the single switch the Python layer consults.
+The library is plain C ABI (``include/igg_b200.h``); tensors cross the boundary as raw device
+pointers and the current ``torch`` CUDA stream.  ``available()`` is the single switch the Python
+layer consults: it is true when the shared object loads **and** a CUDA device is present.  On a
+GPU machine a missing library is an error, not a silent fallback (``require()``).
 """
 from __future__ import annotations
 
+import ctypes as C
+import os
+from typing import Optional, Sequence
+
+import torch
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_lib", "libigg_b200.so")
+_lib = None
+_load_error: Optional[str] = None
+
+ERR_INVALID, ERR_UNSUPPORTED, ERR_TIMEOUT = -1, -2, -3
+FLAG_BANKS, BANK_STRIDE = 32, 64
+SLOT_DATA, SLOT_READY, SLOT_ERR, SLOT_CTA_COUNT = 0, 27, 54, 55
+MAX_HALO_FIELDS = 8
+
+c_f64p = C.c_void_p
+c_u64p = C.c_void_p
+
+
+class Push2D(C.Structure):
+    _fields_ = [("peer_dst", C.c_void_p * 9), ("peer_flag", C.c_void_p * 9), ("my_flag", C.c_void_p * 9),
+                ("my_count", C.c_void_p * 9), ("err_word", C.c_void_p), ("epoch", C.c_uint64)]
+
+
+class Push3D(C.Structure):
+    _fields_ = [("peer_dst", C.c_void_p * 27), ("peer_flag", C.c_void_p * 27), ("my_flag", C.c_void_p * 27),
+                ("my_count", C.c_void_p * 27), ("err_word", C.c_void_p), ("epoch", C.c_uint64)]
+
+
+class HaloXfer(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("n", C.c_int * 3), ("src_start", C.c_int * 3),
+                ("dst_start", C.c_int * 3), ("extent", C.c_int * 3)]
+
+
+class HaloSync(C.Structure):
+    _fields_ = [("peer_bank", C.c_void_p * 27), ("my_bank", C.c_void_p), ("my_count_bank", C.c_void_p),
+                ("epoch", C.c_uint64)]
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def _declare(lib) -> None:
+    i, d, vp, sz, u64 = C.c_int, C.c_double, C.c_void_p, C.c_size_t, C.c_uint64
+    sig = {
+        "igg_version": ([], i),
+        "igg_last_error": ([], C.c_char_p),
+        "igg_device_info": ([C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(sz)], i),
+        "igg_launch_count": ([], C.c_ulonglong),
+        "igg_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d, vp, i, i, i, i, C.POINTER(Push2D), vp], i),
+        "igg_flux2d": ([vp, vp, vp, i, i, d, d, d, vp], i),
+        "igg_residual2d": ([vp, vp, vp, vp, i, i, d, d, vp], i),
+        "igg_update2d": ([vp, vp, i, i, d, C.POINTER(Push2D), vp], i),
+        "igg_diffusion3d_step": ([vp, vp, vp, i, i, i, d, d, d, d, d, i, i, i, i, i, C.POINTER(Push3D), vp], i),
+        "igg_gaussian_ic2d": ([vp, i, i, d, d, d, d, d, d, vp], i),
+        "igg_gaussian_ic3d": ([vp, i, i, i, d, d, d, d, d, d, d, d, d, vp], i),
+        "igg_pack_plane": ([vp, i, i, i, i, i, vp, vp], i),
+        "igg_unpack_plane": ([vp, i, i, i, i, i, vp, vp], i),
+        "igg_extract_inner": ([vp, i, i, i, vp, vp], i),
+        "igg_fabric_alloc": ([sz, C.POINTER(vp)], i),
+        "igg_fabric_free": ([vp], i),
+        "igg_ipc_export": ([vp, vp, C.POINTER(u64)], i),
+        "igg_ipc_open": ([vp, C.POINTER(vp)], i),
+        "igg_ipc_close": ([vp], i),
+        "igg_can_access_peer": ([i, i, C.POINTER(i)], i),
+        "igg_halo_exchange_peer": ([vp, i, C.POINTER(HaloSync), vp], i),
+        "igg_neighbor_barrier": ([C.POINTER(HaloSync), vp], i),
+        "igg_wait_epoch": ([C.POINTER(HaloSync), vp], i),
+        "igg_peer_copy": ([vp, vp, sz, vp, u64, vp, vp], i),
+        "igg_wait_value": ([vp, u64, vp, vp], i),
+        "igg_reduce_scratch_bytes": ([sz], sz),
+        "igg_reduce_max_sum": ([vp, sz, vp, vp, vp], i),
+        "igg_colormap": ([vp, sz, d, d, vp, vp, vp], i),
+        "igg_cpu_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d], i),
+        "igg_cpu_diffusion2d_run": ([vp, vp, vp, i, i, d, d, d, d, i], i),
+    }
+    for name, (argtypes, restype) in sig.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = restype
+
+
+def load(build_if_missing: bool = False):
+    """Load (once) and return the ctypes library handle, or ``None`` if it cannot be loaded."""
+    global _lib, _load_error
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH) and build_if_missing:
+        from .. import build as _build
+        _build.build()
+    try:
+        lib = C.CDLL(_LIB_PATH)
+        _declare(lib)
+        _lib = lib
+    except (OSError, AttributeError) as e:  # missing file or stale library without a symbol
+        _load_error = str(e)
+        _lib = None
+    return _lib
+
+
+def loaded() -> bool:
+    return load() is not None
+
 
 def available() -> bool:
-    return False
+    """True when the CUDA kernels can run: library loaded and a CUDA device present."""
+    return torch.cuda.is_available() and load() is not None
+
+
+def require():
+    """The native library, or a loud error (used on every GPU path: no silent PyTorch fallback)."""
+    lib = load()
+    if lib is None:
+        raise NativeError(f"native library {_LIB_PATH} is not loadable ({_load_error}); "
+                          "build it with `python -m rocm_mpi_b200.build`")
+    return lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        msg = require().igg_last_error().decode(errors="replace")
+        raise NativeError(f"native call failed (rc={rc}): {msg}")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _f64(t: torch.Tensor, name: str = "tensor") -> int:
+    if t.dtype != torch.float64 or not t.is_cuda or not t.is_contiguous():
+        raise TypeError(f"{name} must be a contiguous CUDA float64 tensor "
+                        f"(got {t.dtype}, {t.device}, contiguous={t.is_contiguous()})")
+    return t.data_ptr()
+
+
+def launch_count() -> int:
+    lib = load()
+    return int(lib.igg_launch_count()) if lib is not None else 0
+
+
+def device_info() -> dict:
+    lib = require()
+    sm, ma, mi, sh = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
+    _check(lib.igg_device_info(C.byref(sm), C.byref(ma), C.byref(mi), C.byref(sh)))
+    return {"sm_count": sm.value, "cc": (ma.value, mi.value), "smem_optin": sh.value}
+
+
+# ---- stencils ---------------------------------------------------------------------------------------
+VARIANTS = {"direct": 0, "tma": 1}
+
+
+def diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
+                     _dy: float, mode: int = 0, b_width: Sequence[int] = (1, 1), variant: str = "tma",
+                     push: Optional[Push2D] = None, dev_params: Optional[torch.Tensor] = None) -> None:
+    """``T2 <- step(T)``; see ``igg_diffusion2d_step`` in ``include/igg_b200.h``.
+
+    ``dev_params``: optional device tensor ``[lam, dt, _dx, _dy]`` overriding the scalar arguments."""
+    lib = require()
+    nx, ny = T.shape
+    if T2.shape != T.shape or Cp.shape != T.shape:
+        raise ValueError("T, T2 and Cp must have the same shape")
+    _check(lib.igg_diffusion2d_step(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
+                                    _f64(dev_params, "dev_params") if dev_params is not None else None,
+                                    mode, int(b_width[0]), int(b_width[1]), VARIANTS[variant],
+                                    C.byref(push) if push is not None else None, _stream()))
+
+
+def diffusion3d_step(T2, T, Cp, lam, dt, _dx, _dy, _dz, mode: int = 0, b_width=(1, 1, 1), variant: str = "tma",
+                     push: Optional[Push3D] = None) -> None:
+    lib = require()
+    nx, ny, nz = T.shape
+    if T2.shape != T.shape or Cp.shape != T.shape:
+        raise ValueError("T, T2 and Cp must have the same shape")
+    _check(lib.igg_diffusion3d_step(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, nz, lam, dt, _dx, _dy,
+                                    _dz, mode, int(b_width[0]), int(b_width[1]), int(b_width[2]),
+                                    VARIANTS[variant], C.byref(push) if push is not None else None, _stream()))
+
+
+def flux2d(qx, qy, T, lam, _dx, _dy) -> None:
+    nx, ny = T.shape
+    if tuple(qx.shape) != (nx - 1, ny - 2) or tuple(qy.shape) != (nx - 2, ny - 1):
+        raise ValueError("qx must be (nx-1, ny-2) and qy (nx-2, ny-1)")
+    _check(require().igg_flux2d(_f64(qx), _f64(qy), _f64(T), nx, ny, lam, _dx, _dy, _stream()))
+
+
+def residual2d(dTdt, qx, qy, Cp, _dx, _dy) -> None:
+    nx, ny = Cp.shape
+    if tuple(dTdt.shape) != (nx - 2, ny - 2):
+        raise ValueError("dTdt must be (nx-2, ny-2)")
+    _check(require().igg_residual2d(_f64(dTdt), _f64(qx), _f64(qy), _f64(Cp), nx, ny, _dx, _dy, _stream()))
+
+
+def update2d(T, dTdt, dt, push: Optional[Push2D] = None) -> None:
+    nx, ny = T.shape
+    _check(require().igg_update2d(_f64(T), _f64(dTdt), nx, ny, dt, C.byref(push) if push is not None else None,
+                                  _stream()))
+
+
+def gaussian_ic_2d(T, x0, y0, dx, dy, lx, ly) -> None:
+    nx, ny = T.shape
+    _check(require().igg_gaussian_ic2d(_f64(T), nx, ny, x0, y0, dx, dy, lx, ly, _stream()))
+
+
+def gaussian_ic_3d(T, x0, y0, z0, dx, dy, dz, lx, ly, lz) -> None:
+    nx, ny, nz = T.shape
+    _check(require().igg_gaussian_ic3d(_f64(T), nx, ny, nz, x0, y0, z0, dx, dy, dz, lx, ly, lz, _stream()))
+
+
+# ---- halo helpers -----------------------------------------------------------------------------------
+def _shape3(A: torch.Tensor):
+    s = list(A.shape) + [1] * (3 - A.dim())
+    return s[0], s[1], s[2]
+
+
+def pack_plane(A, dim: int, idx: int, out) -> None:
+    n0, n1, n2 = _shape3(A)
+    _check(require().igg_pack_plane(_f64(A), n0, n1, n2, dim, idx, _f64(out), _stream()))
+
+
+def unpack_plane(A, dim: int, idx: int, src) -> None:
+    n0, n1, n2 = _shape3(A)
+    _check(require().igg_unpack_plane(_f64(A), n0, n1, n2, dim, idx, _f64(src), _stream()))
+
+
+def extract_inner(A, out=None) -> torch.Tensor:
+    n0, n1, n2 = _shape3(A)
+    shape = tuple(s - 2 if s > 2 else s for s in A.shape)
+    if out is None:
+        out = torch.empty(shape, dtype=A.dtype, device=A.device)
+    _check(require().igg_extract_inner(_f64(A), n0, n1, n2, _f64(out), _stream()))
+    return out
+
+
+# ---- diagnostics ------------------------------------------------------------------------------------
+_reduce_ws = {}
+
+
+def reduce_max_sum(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Device tensor ``[max, sum]`` of ``x`` (asynchronous; scratch is cached per device)."""
+    lib = require()
+    dev = x.device.index
+    ws = _reduce_ws.get(dev)
+    if ws is None:
+        ws = torch.zeros(int(lib.igg_reduce_scratch_bytes(x.numel())), dtype=torch.uint8, device=x.device)
+        _reduce_ws[dev] = ws
+    if out is None:
+        out = torch.empty(2, dtype=torch.float64, device=x.device)
+    _check(lib.igg_reduce_max_sum(_f64(x), x.numel(), ws.data_ptr(), _f64(out), _stream()))
+    return out
+
+
+def colormap(field: torch.Tensor, vmin: float, vmax: float, lut: torch.Tensor) -> torch.Tensor:
+    lib = require()
+    lut_d = lut.to(device=field.device, dtype=torch.uint8).contiguous()
+    rgb = torch.empty(tuple(field.shape) + (3,), dtype=torch.uint8, device=field.device)
+    _check(lib.igg_colormap(_f64(field.contiguous()), field.numel(), vmin, vmax, lut_d.data_ptr(), rgb.data_ptr(),
+                            _stream()))
+    return rgb
+
+
+# ---- CPU restatement --------------------------------------------------------------------------------
+def cpu_diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam, dt, _dx, _dy) -> None:
+    lib = require()
+    for t in (T2, T, Cp):
+        if t.is_cuda or t.dtype != torch.float64 or not t.is_contiguous():
+            raise TypeError("cpu_diffusion2d_step needs contiguous CPU float64 tensors")
+    nx, ny = T.shape
+    _check(lib.igg_cpu_diffusion2d_step(T.data_ptr(), T2.data_ptr(), Cp.data_ptr(), nx, ny, lam, dt, _dx, _dy))
+
+
+def cpu_diffusion2d_run(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam, dt, _dx, _dy, nt: int) -> None:
+    lib = require()
+    nx, ny = T.shape
+    _check(lib.igg_cpu_diffusion2d_run(T.data_ptr(), T2.data_ptr(), Cp.data_ptr(), nx, ny, lam, dt, _dx, _dy, nt))

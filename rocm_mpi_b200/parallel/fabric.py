@@ -1,0 +1,363 @@
+"""Peer-memory fabric: symmetric device buffers, flag pads and the engines built on them.
+
+Where the reference relies on a ROCm-aware MPI that accepts device pointers
+(``MPI.Sendrecv!`` on ``ROCArray``s, ``scripts/rocmaware_test_selectdevice.jl:15-22``; the
+``IGG_ROCMAWARE_MPI=1`` mode of ``update_halo!``, ``scripts/setenv.sh:11-13``), a B200 node lets
+every GPU address every other GPU's memory through NVSwitch.  The fabric therefore
+
+* allocates (or registers) fields so that every rank can obtain a **peer-mapped pointer** to the
+  same field on each Cartesian neighbour (CUDA IPC handles travel once over gloo);
+* owns a **flag pad** per rank -- ``FLAG_BANKS`` independent banks of epoch flags that neighbours
+  write with system-scope release stores -- plus a private pad of arrival counters;
+* provides :class:`PeerHalo` (``update_halo`` as ONE kernel launch: handshake, all boxes stored
+  into the neighbours' arrays, epoch released, own epoch awaited) and :class:`PushPlan` (the
+  descriptor that lets the stencil kernels push their edge cells themselves).
+
+With a single process (no launcher) every neighbour of a periodic grid is the rank itself and the
+same kernels run against local pointers, which is how the protocol is tested on one GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import itertools
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from ..ops import native
+from .grid import GlobalGrid, global_grid
+from .halo import halo_boxes, halo_planes
+from .topology import NDIMS, PROC_NULL
+
+__all__ = ["Fabric", "PeerHalo", "PushPlan", "get_fabric", "fabric_zeros", "offset_slot", "neighbor_offsets"]
+
+
+def offset_slot(o: Sequence[int]) -> int:
+    """Slot index of neighbour offset ``(ox, oy, oz)`` in a flag bank."""
+    return ((o[0] + 1) * 3 + (o[1] + 1)) * 3 + (o[2] + 1)
+
+
+class _DeviceBlock:
+    """Exposes a raw device allocation to ``torch.as_tensor`` via ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr: int, shape: Tuple[int, ...], typestr: str) -> None:
+        self.ptr = ptr
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (ptr, False),
+                                         "version": 3, "strides": None}
+
+
+_TYPESTR = {torch.float64: "<f8", torch.float32: "<f4", torch.int64: "<i8", torch.uint8: "|u1"}
+
+
+def neighbor_offsets(g: GlobalGrid) -> List[Tuple[Tuple[int, int, int], int]]:
+    """All ``(offset, rank)`` pairs of existing Cartesian neighbours (up to 26)."""
+    out = []
+    rng = [(-1, 0, 1) if g.nxyz[d] > 1 else (0,) for d in range(NDIMS)]
+    for o in itertools.product(*rng):
+        if o == (0, 0, 0):
+            continue
+        r = g.topo.rank_at_offset(o)
+        if r != PROC_NULL:
+            out.append((o, r))
+    return out
+
+
+class Fabric:
+    """Per-grid registry of peer-mapped memory."""
+
+    def __init__(self, g: GlobalGrid) -> None:
+        if g.device_type != "cuda":
+            raise RuntimeError("the peer fabric needs CUDA devices")
+        self.g = g
+        self.lib = native.require()
+        self._owned: List[int] = []                     # pointers from igg_fabric_alloc
+        self._opened: Dict[bytes, int] = {}             # IPC handle -> mapped base pointer
+        self._peer_ptrs: Dict[int, Dict[int, int]] = {}  # local data_ptr -> {rank: peer pointer}
+        self._keepalive: List[object] = []
+        self.neighbors = neighbor_offsets(g)
+        self.neighbor_ranks = sorted({r for _, r in self.neighbors})
+        self._next_bank = 0
+        pad_elems = native.FLAG_BANKS * native.BANK_STRIDE
+        self.flag_pad = self.zeros((pad_elems,), torch.int64)       # collective
+        self.count_pad = torch.zeros(pad_elems, dtype=torch.int64, device=g.device)
+        self._check_peer_access()
+
+    # -- allocation / registration --------------------------------------------------------------
+    def _check_peer_access(self) -> None:
+        if self.g.nprocs == 1:
+            return
+        # ranks on one node map 1:1 to devices (select_device); make sure NVLink/P2P is there
+        me_dev = self.g.device.index
+        devs = self.g.comm.allgather_object(me_dev)
+        for r in self.neighbor_ranks:
+            if r == self.g.me:
+                continue
+            can = C.c_int(0)
+            native._check(self.lib.igg_can_access_peer(me_dev, devs[r], C.byref(can)))
+            if not can.value:
+                raise RuntimeError(f"GPU {me_dev} cannot access peer GPU {devs[r]} (rank {r}); "
+                                   "use transport='nccl'")
+
+    def zeros(self, shape: Sequence[int], dtype: torch.dtype = torch.float64) -> torch.Tensor:
+        """Collective: allocate a zero-filled symmetric tensor, addressable by all neighbours."""
+        shape = tuple(int(s) for s in shape)
+        numel = 1
+        for s in shape:
+            numel *= s
+        nbytes = max(numel * torch.empty((), dtype=dtype).element_size(), 16)
+        ptr = C.c_void_p()
+        native._check(self.lib.igg_fabric_alloc(nbytes, C.byref(ptr)))
+        self._owned.append(ptr.value)
+        blk = _DeviceBlock(ptr.value, shape, _TYPESTR[dtype])
+        t = torch.as_tensor(blk, device=self.g.device)
+        if t.data_ptr() != ptr.value:
+            raise RuntimeError("torch did not alias the fabric allocation")
+        self._keepalive.append(blk)
+        self.register(t)
+        return t
+
+    def register(self, t: torch.Tensor) -> None:
+        """Collective: make ``t`` addressable by the neighbours (no-op if already registered)."""
+        key = t.data_ptr()
+        if key in self._peer_ptrs:
+            return
+        g = self.g
+        if g.nprocs == 1:
+            self._peer_ptrs[key] = {0: key}
+            return
+        handle = (C.c_ubyte * 64)()
+        off = C.c_uint64(0)
+        try:
+            native._check(self.lib.igg_ipc_export(key, handle, C.byref(off)))
+        except native.NativeError as e:
+            raise RuntimeError("cannot export this tensor over CUDA IPC (allocate it with "
+                               "rocm_mpi_b200.zeros(..., symmetric=True), or do not use expandable "
+                               f"segments): {e}") from e
+        infos = g.comm.allgather_object((bytes(handle), int(off.value)))
+        ptrs = {g.me: key}
+        for r in self.neighbor_ranks:
+            if r == g.me:
+                continue
+            h, o = infos[r]
+            base = self._opened.get(h)
+            if base is None:
+                out = C.c_void_p()
+                native._check(self.lib.igg_ipc_open(h, C.byref(out)))
+                base = out.value
+                self._opened[h] = base
+            ptrs[r] = base + o
+        self._peer_ptrs[key] = ptrs
+
+    def is_registered(self, t: torch.Tensor) -> bool:
+        return t.data_ptr() in self._peer_ptrs
+
+    def peer_ptr(self, t: torch.Tensor, rank: int) -> int:
+        return self._peer_ptrs[t.data_ptr()][rank]
+
+    # -- flag banks -----------------------------------------------------------------------------
+    def new_bank(self) -> int:
+        if self._next_bank >= native.FLAG_BANKS:
+            raise RuntimeError("out of flag banks")
+        b = self._next_bank
+        self._next_bank += 1
+        return b
+
+    def bank_ptr(self, bank: int, rank: Optional[int] = None) -> int:
+        base = self.flag_pad.data_ptr() if rank is None else self.peer_ptr(self.flag_pad, rank)
+        return base + bank * native.BANK_STRIDE * 8
+
+    def count_bank_ptr(self, bank: int) -> int:
+        return self.count_pad.data_ptr() + bank * native.BANK_STRIDE * 8
+
+    def sync_struct(self, bank: int, epoch: int, offsets: Optional[Sequence] = None) -> native.HaloSync:
+        s = native.HaloSync()
+        for (o, r) in (self.neighbors if offsets is None else offsets):
+            s.peer_bank[offset_slot(o)] = self.bank_ptr(bank, r)
+        s.my_bank = self.bank_ptr(bank)
+        s.my_count_bank = self.count_bank_ptr(bank)
+        s.epoch = epoch
+        return s
+
+    def check_errors(self, bank: int) -> None:
+        """Synchronise and raise if a flag wait on ``bank`` timed out."""
+        torch.cuda.current_stream().synchronize()
+        v = int(self.flag_pad[bank * native.BANK_STRIDE + native.SLOT_ERR].item())
+        if v != 0:
+            self.flag_pad[bank * native.BANK_STRIDE + native.SLOT_ERR] = 0
+            raise RuntimeError(f"peer flag wait timed out on bank {bank} (word {v & ((1 << 63) - 1)}); "
+                               "a neighbour did not reach the matching call")
+
+    def close(self) -> None:
+        torch.cuda.synchronize()
+        self.g.comm.barrier()
+        for base in self._opened.values():
+            self.lib.igg_ipc_close(base)
+        self._opened.clear()
+        self._peer_ptrs.clear()
+        # owned blocks stay alive while torch tensors alias them; free them only at process exit
+        # unless nothing references them any more (the tensors are views on raw pointers)
+        self._keepalive.clear()
+
+
+def get_fabric(g: Optional[GlobalGrid] = None) -> Fabric:
+    g = g or global_grid()
+    fab = g.cache.get("fabric")
+    if fab is None:
+        fab = Fabric(g)
+        g.cache["fabric"] = fab
+    return fab
+
+
+def fabric_zeros(shape: Sequence[int], dtype: torch.dtype = torch.float64) -> torch.Tensor:
+    """Collective allocation of a field in peer-addressable memory."""
+    return get_fabric().zeros(shape, dtype)
+
+
+# =====================================================================================================
+class PeerHalo:
+    """``update_halo`` over peer memory: one kernel launch per call (transport ``peer``)."""
+
+    def __init__(self, g: GlobalGrid) -> None:
+        self.g = g
+        self.fab = get_fabric(g)
+        self.bank = self.fab.new_bank()
+        self.epoch = 0
+        self._tables: Dict[tuple, Tuple[torch.Tensor, int]] = {}
+        self.launches = 0
+
+    def _boxes(self, A: torch.Tensor):
+        """``(offset, rank, src_start, dst_start, extent)`` of every neighbour box (see ``halo_boxes``)."""
+        g = self.g
+        ranks = dict(self.fab.neighbors)
+        has_nb = lambda side, d: g.neighbors[side][d] != PROC_NULL
+        for (o, src, dst, ext) in halo_boxes(g.nxyz, g.overlaps, A.shape, has_nb, list(ranks)):
+            yield o, ranks[o], src, dst, ext
+
+    def _table(self, fields: Sequence[torch.Tensor]):
+        key = tuple((A.data_ptr(), tuple(A.shape)) for A in fields)
+        hit = self._tables.get(key)
+        if hit is not None:
+            return hit
+        for A in fields:
+            if A.dtype != torch.float64:
+                raise TypeError("the peer transport moves float64 fields")
+            self.fab.register(A)          # collective on first sight of a field
+        xf: List[native.HaloXfer] = []
+        for A in fields:
+            shape = list(A.shape) + [1] * (NDIMS - A.dim())
+            for (o, r, src, dst, ext) in self._boxes(A):
+                x = native.HaloXfer()
+                x.src = A.data_ptr()
+                x.dst = self.fab.peer_ptr(A, r)
+                for d in range(3):
+                    x.n[d] = shape[d]
+                    x.src_start[d] = src[d]
+                    x.dst_start[d] = dst[d]
+                    x.extent[d] = ext[d]
+                xf.append(x)
+        n = len(xf)
+        if n:
+            arr = (native.HaloXfer * n)(*xf)
+            host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+            dev = host.to(self.g.device)
+        else:
+            dev = torch.zeros(16, dtype=torch.uint8, device=self.g.device)
+        self._tables[key] = (dev, n)
+        if len(self._tables) > 64:
+            self._tables.pop(next(iter(self._tables)))
+        return dev, n
+
+    def update(self, fields: Sequence[torch.Tensor]) -> None:
+        dev, n = self._table(fields)
+        if not self.fab.neighbors:
+            return
+        self.epoch += 1
+        sync = self.fab.sync_struct(self.bank, self.epoch)
+        native._check(self.fab.lib.igg_halo_exchange_peer(dev.data_ptr(), n, C.byref(sync), native._stream()))
+        self.launches += 1
+
+    def close(self) -> None:
+        self._tables.clear()
+
+
+# =====================================================================================================
+class PushPlan:
+    """Descriptor factory for stencil kernels that push their own edge cells (2-D and 3-D).
+
+    Usage per time loop::
+
+        plan = PushPlan(T, T2)       # collective (registers the fields, takes a flag bank)
+        plan.begin()                 # halos made consistent + neighbour barrier
+        for it in range(nt):
+            native.diffusion2d_step(T2, T, Cp, ..., push=plan.next(T2))   # pushes INTO T2's peers
+            T, T2 = T2, T
+        plan.finish()                # all incoming pushes have landed; error word checked
+    """
+
+    def __init__(self, *fields: torch.Tensor) -> None:
+        g = global_grid()
+        self.g = g
+        self.fab = get_fabric(g)
+        self.bank = self.fab.new_bank()
+        self.epoch = 0
+        self.fields = fields
+        self.ndim = fields[0].dim()
+        if self.ndim not in (2, 3):
+            raise ValueError("PushPlan supports 2-D and 3-D fields")
+        for A in fields:
+            if tuple(A.shape) != tuple(g.nxyz[:self.ndim]):
+                raise ValueError("pushed fields must have the local grid size (no staggering)")
+            self.fab.register(A)
+        self._desc: Dict[int, object] = {}
+        for A in fields:
+            self._desc[A.data_ptr()] = self._build(A)
+        self._active = False
+
+    def _build(self, A: torch.Tensor):
+        fab, bank = self.fab, self.bank
+        my_bank, cnt_bank = fab.bank_ptr(bank), fab.count_bank_ptr(bank)
+        d = native.Push2D() if self.ndim == 2 else native.Push3D()
+        for (o, r) in fab.neighbors:
+            k3 = offset_slot(o)
+            k = (o[0] + 1) * 3 + (o[1] + 1) if self.ndim == 2 else k3
+            d.peer_dst[k] = fab.peer_ptr(A, r)
+            d.peer_flag[k] = fab.bank_ptr(bank, r) + (native.SLOT_DATA + (26 - k3)) * 8
+            d.my_flag[k] = my_bank + (native.SLOT_DATA + k3) * 8
+            d.my_count[k] = cnt_bank + k3 * 8
+        d.err_word = my_bank + native.SLOT_ERR * 8
+        d.epoch = 0
+        return d
+
+    def begin(self, sync_halos: bool = True) -> None:
+        """Make the halos of all plan fields consistent, then barrier with the neighbours."""
+        from .halo import update_halo
+        if sync_halos:
+            update_halo(*self.fields, transport="peer")
+        b = self.bank * native.BANK_STRIDE
+        self.fab.count_pad[b:b + native.BANK_STRIDE].zero_()
+        if self.fab.neighbors:
+            self.g.comm.barrier()      # hosts first, so the device barrier below never waits long
+            self.epoch += 1
+            sync = self.fab.sync_struct(self.bank, self.epoch)
+            native._check(self.fab.lib.igg_neighbor_barrier(C.byref(sync), native._stream()))
+        self._active = True
+
+    def next(self, dst: torch.Tensor):
+        """Descriptor for the next step, whose results are written to ``dst`` (and its peers)."""
+        if not self._active:
+            raise RuntimeError("PushPlan.begin() must be called before the time loop")
+        if not self.fab.neighbors:
+            return None
+        self.epoch += 1
+        d = self._desc[dst.data_ptr()]
+        d.epoch = self.epoch
+        return d
+
+    def finish(self, check: bool = True) -> None:
+        """Wait until every neighbour's pushes of the last epoch have landed here."""
+        if self.fab.neighbors and self._active:
+            sync = self.fab.sync_struct(self.bank, self.epoch)
+            native._check(self.fab.lib.igg_wait_epoch(C.byref(sync), native._stream()))
+        self._active = False
+        if check:
+            self.fab.check_errors(self.bank)

@@ -37,7 +37,7 @@ import torch
 from .grid import GlobalGrid, global_grid
 from .topology import NDIMS, PROC_NULL
 
-__all__ = ["update_halo", "halo_planes", "HaloSpec", "default_transport", "ExchangeHalo"]
+__all__ = ["update_halo", "halo_planes", "halo_boxes", "HaloSpec", "default_transport", "ExchangeHalo"]
 
 
 @dataclass(frozen=True)
@@ -60,6 +60,49 @@ def halo_planes(nxyz: Sequence[int], overlaps: Sequence[int], shape: Sequence[in
             continue
         specs.append(HaloSpec(dim=dim, send=(o - 1, size - o), recv=(0, size - 1)))
     return specs
+
+
+def halo_boxes(nxyz: Sequence[int], overlaps: Sequence[int], shape: Sequence[int], has_neighbor,
+               offsets: Sequence[Sequence[int]]):
+    """The dimension-sequential exchange written as independent box copies, one per neighbour offset.
+
+    Exchanging x, then y, then z with full-extent planes delivers to every halo cell the *original*
+    value of exactly one remote cell: shift by -1/+1 in each dimension where the cell is a halo cell
+    with a neighbour.  Such source cells are never themselves received, so all boxes can be copied
+    concurrently.  For offset ``o``: in dimensions with ``o[d] != 0`` the box is the single send plane
+    (landing in the neighbour's receive plane); in dimensions with ``o[d] == 0`` it spans every index
+    that is not a receive plane with a neighbour.  ``has_neighbor(side, dim) -> bool``.
+
+    Yields ``(offset, src_start, dst_start, extent)``; this is what the one-launch peer-memory
+    ``update_halo`` executes (``csrc/fabric.cu``), and ``tests/test_halo_virtual.py`` checks it against
+    the sequential definition.
+    """
+    specs = halo_planes(nxyz, overlaps, shape)
+    shp = list(shape) + [1] * (NDIMS - len(shape))
+    for o in offsets:
+        if all(x == 0 for x in o):
+            continue
+        src, dst, ext = [0, 0, 0], [0, 0, 0], [1, 1, 1]
+        ok = True
+        for d in range(NDIMS):
+            sp = specs[d]
+            if o[d] != 0:
+                side = 0 if o[d] < 0 else 1
+                if sp is None or not has_neighbor(side, d):
+                    ok = False
+                    break
+                src[d], dst[d], ext[d] = sp.send[side], sp.recv[1 - side], 1
+            else:
+                lo, hi = 0, shp[d]
+                if sp is not None:
+                    if has_neighbor(0, d):
+                        lo = 1
+                    if has_neighbor(1, d):
+                        hi = shp[d] - 1
+                src[d] = dst[d] = lo
+                ext[d] = hi - lo
+        if ok and all(e > 0 for e in ext):
+            yield tuple(o), tuple(src), tuple(dst), tuple(ext)
 
 
 def default_transport(field: torch.Tensor) -> str:

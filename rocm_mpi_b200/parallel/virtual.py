@@ -13,7 +13,7 @@ from typing import List, Sequence
 
 import torch
 
-from .halo import halo_planes
+from .halo import halo_boxes, halo_planes
 from .topology import NDIMS, PROC_NULL, CartTopology, cart_coords
 
 __all__ = ["VirtualGrid"]
@@ -67,6 +67,24 @@ class VirtualGrid:
                             planes[(nb, 1 - side)] = locs[r].select(dim, spec.send[side]).clone()
                 for (r, side), p in planes.items():
                     locs[r].select(dim, spec.recv[side]).copy_(p)
+
+    def update_halo_boxes(self, *fields: List[torch.Tensor]) -> None:
+        """Same result as :meth:`update_halo`, computed the way the peer-memory kernel does it:
+        all boxes read from the pre-exchange state, one box per neighbour offset."""
+        import itertools
+        for locs in fields:
+            before = [L.clone() for L in locs]
+            for r in range(self.nprocs):
+                topo = self.topos[r]
+                rng = [(-1, 0, 1) if self.nxyz[d] > 1 else (0,) for d in range(NDIMS)]
+                offs = [o for o in itertools.product(*rng) if topo.rank_at_offset(o) != PROC_NULL]
+                has_nb = lambda side, d, t=topo: t.neighbors[side][d] != PROC_NULL
+                for (o, src, dst, ext) in halo_boxes(self.nxyz, self.overlaps, locs[r].shape, has_nb, offs):
+                    nb = topo.rank_at_offset(o)
+                    nd = locs[r].dim()
+                    ssl = tuple(slice(src[d], src[d] + ext[d]) for d in range(nd))
+                    dsl = tuple(slice(dst[d], dst[d] + ext[d]) for d in range(nd))
+                    locs[nb][dsl] = before[r][ssl]
 
     # -- gather ------------------------------------------------------------------------
     def gather(self, blocks: List[torch.Tensor]) -> torch.Tensor:

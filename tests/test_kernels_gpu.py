@@ -1,0 +1,188 @@
+"""GPU numerics: every native kernel against a plain PyTorch fp64 statement of the same op."""
+import pytest
+import torch
+
+import rocm_mpi_b200 as igg
+from rocm_mpi_b200.ops import native, reference as ref
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-13
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _need_native():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    native.require()
+
+
+def _fields(nx, ny, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    T = torch.rand(nx, ny, generator=g, dtype=torch.float64)
+    Cp = torch.rand(nx, ny, generator=g, dtype=torch.float64) + 0.5
+    return T, Cp
+
+
+@pytest.mark.parametrize("variant", ["direct", "tma"])
+@pytest.mark.parametrize("shape", [(64, 64), (130, 258), (33, 130), (257, 512), (3, 4), (40, 1026)])
+def test_fused_step_matches_reference(variant, shape):
+    nx, ny = shape
+    T, Cp = _fields(nx, ny)
+    want = T.clone()
+    ref.perf_step(want, T, Cp, 1.3, 1e-3, 2.0, 3.0)
+    Td, Cpd = T.cuda(), Cp.cuda()
+    T2d = Td.clone()
+    n0 = native.launch_count()
+    native.diffusion2d_step(T2d, Td, Cpd, 1.3, 1e-3, 2.0, 3.0, variant=variant)
+    assert native.launch_count() == n0 + 1
+    assert float((T2d.cpu() - want).abs().max()) < TOL
+    # boundary cells of T2 are never written
+    assert torch.equal(T2d.cpu()[0], T[0]) and torch.equal(T2d.cpu()[:, -1], T[:, -1])
+
+
+def test_direct_variant_handles_odd_ny_and_tma_rejects_it():
+    T, Cp = _fields(50, 131)
+    want = T.clone()
+    ref.perf_step(want, T, Cp, 1.0, 1e-3, 2.0, 3.0)
+    T2d = T.cuda().clone()
+    native.diffusion2d_step(T2d, T.cuda(), Cp.cuda(), 1.0, 1e-3, 2.0, 3.0, variant="direct")
+    assert float((T2d.cpu() - want).abs().max()) < TOL
+    with pytest.raises(native.NativeError):
+        native.diffusion2d_step(T2d, T.cuda(), Cp.cuda(), 1.0, 1e-3, 2.0, 3.0, variant="tma")
+
+
+@pytest.mark.parametrize("variant", ["direct", "tma"])
+@pytest.mark.parametrize("shape,bw", [((200, 520), (16, 4)), ((70, 300), (32, 8)), ((40, 40), (30, 30)),
+                                      ((300, 260), (1, 1))])
+def test_split_step_frame_then_interior(variant, shape, bw):
+    nx, ny = shape
+    T, Cp = _fields(nx, ny, 3)
+    full = T.clone()
+    ref.perf_step(full, T, Cp, 1.0, 2e-3, 1.5, 2.5)
+    m = ref.frame_mask(T.shape, bw)
+    Td, Cpd = T.cuda(), Cp.cuda()
+    T2d = Td.clone()
+    native.diffusion2d_step(T2d, Td, Cpd, 1.0, 2e-3, 1.5, 2.5, mode=1, b_width=bw, variant=variant)
+    got = T2d.cpu()
+    assert float((got[m] - full[m]).abs().max()) < TOL          # frame computed
+    assert torch.equal(got[~m], T[~m])                           # everything else untouched
+    native.diffusion2d_step(T2d, Td, Cpd, 1.0, 2e-3, 1.5, 2.5, mode=2, b_width=bw, variant=variant)
+    assert float((T2d.cpu() - full).abs().max()) < TOL          # frame + interior == full step
+
+
+def test_dev_params_override_scalars():
+    T, Cp = _fields(66, 130, 5)
+    want = T.clone()
+    ref.perf_step(want, T, Cp, 0.7, 3e-3, 2.0, 3.0)
+    params = torch.tensor([0.7, 3e-3, 2.0, 3.0], dtype=torch.float64, device="cuda")
+    for variant in ("direct", "tma"):
+        T2d = T.cuda().clone()
+        native.diffusion2d_step(T2d, T.cuda(), Cp.cuda(), 9.0, 9.0, 9.0, 9.0, variant=variant, dev_params=params)
+        assert float((T2d.cpu() - want).abs().max()) < TOL
+
+
+def test_kp_kernels_match_reference():
+    nx, ny = 77, 101
+    T, Cp = _fields(nx, ny, 7)
+    lam, dt, _dx, _dy = 1.1, 1e-3, 4.0, 5.0
+    qx = torch.zeros(nx - 1, ny - 2, dtype=torch.float64)
+    qy = torch.zeros(nx - 2, ny - 1, dtype=torch.float64)
+    dTdt = torch.zeros(nx - 2, ny - 2, dtype=torch.float64)
+    Tr = T.clone()
+    ref.kp_step(Tr, Cp, qx, qy, dTdt, lam, dt, _dx, _dy)
+    Td, Cpd = T.cuda(), Cp.cuda()
+    qxd, qyd, dd = torch.zeros_like(qx).cuda(), torch.zeros_like(qy).cuda(), torch.zeros_like(dTdt).cuda()
+    native.flux2d(qxd, qyd, Td, lam, _dx, _dy)
+    native.residual2d(dd, qxd, qyd, Cpd, _dx, _dy)
+    native.update2d(Td, dd, dt)
+    assert float((qxd.cpu() - qx).abs().max()) < TOL
+    assert float((qyd.cpu() - qy).abs().max()) < TOL
+    assert float((dd.cpu() - dTdt).abs().max()) < 1e-11   # 1/Cp amplifies rounding differences
+    assert float((Td.cpu() - Tr).abs().max()) < TOL
+
+
+@pytest.mark.parametrize("variant", ["direct", "tma"])
+@pytest.mark.parametrize("shape", [(20, 18, 66), (9, 17, 130), (34, 10, 64), (3, 3, 4)])
+def test_3d_step_matches_reference(variant, shape):
+    g = torch.Generator().manual_seed(11)
+    T = torch.rand(shape, generator=g, dtype=torch.float64)
+    Cp = torch.rand(shape, generator=g, dtype=torch.float64) + 0.5
+    want = T.clone()
+    ref.perf_step_3d(want, T, Cp, 1.2, 1e-3, 2.0, 3.0, 4.0)
+    T2d = T.cuda().clone()
+    native.diffusion3d_step(T2d, T.cuda(), Cp.cuda(), 1.2, 1e-3, 2.0, 3.0, 4.0, variant=variant)
+    assert float((T2d.cpu() - want).abs().max()) < TOL
+
+
+@pytest.mark.parametrize("variant", ["direct", "tma"])
+def test_3d_split_step(variant):
+    shape, bw = (40, 36, 140), (4, 3, 8)
+    g = torch.Generator().manual_seed(12)
+    T = torch.rand(shape, generator=g, dtype=torch.float64)
+    Cp = torch.rand(shape, generator=g, dtype=torch.float64) + 0.5
+    full = T.clone()
+    ref.perf_step_3d(full, T, Cp, 1.0, 1e-3, 2.0, 3.0, 4.0)
+    m = ref.frame_mask(shape, bw)
+    T2d = T.cuda().clone()
+    native.diffusion3d_step(T2d, T.cuda(), Cp.cuda(), 1.0, 1e-3, 2.0, 3.0, 4.0, mode=1, b_width=bw, variant=variant)
+    got = T2d.cpu()
+    assert float((got[m] - full[m]).abs().max()) < TOL
+    assert torch.equal(got[~m], T[~m])
+    native.diffusion3d_step(T2d, T.cuda(), Cp.cuda(), 1.0, 1e-3, 2.0, 3.0, 4.0, mode=2, b_width=bw, variant=variant)
+    assert float((T2d.cpu() - full).abs().max()) < TOL
+
+
+def test_gaussian_ic_matches_host_comprehension():
+    nx, ny, dx, dy = 70, 50, 10.0 / 254, 10.0 / 254
+    T = torch.empty(nx, ny, dtype=torch.float64, device="cuda")
+    native.gaussian_ic_2d(T, 3 * dx, 5 * dy, dx, dy, 10.0, 10.0)
+    xs = (torch.arange(nx, dtype=torch.float64) + 3) * dx
+    ys = (torch.arange(ny, dtype=torch.float64) + 5) * dy
+    want = ref.gaussian_ic(xs, ys, dx, dy, 10.0, 10.0)
+    assert float((T.cpu() - want).abs().max()) < 1e-15
+    T3 = torch.empty(12, 10, 14, dtype=torch.float64, device="cuda")
+    native.gaussian_ic_3d(T3, 0.0, dy, 0.0, dx, dy, dx, 10.0, 10.0, 10.0)
+    want3 = ref.gaussian_ic_3d(torch.arange(12, dtype=torch.float64) * dx,
+                               (torch.arange(10, dtype=torch.float64) + 1) * dy,
+                               torch.arange(14, dtype=torch.float64) * dx, dx, dy, dx, 10.0, 10.0, 10.0)
+    assert float((T3.cpu() - want3).abs().max()) < 1e-15
+
+
+@pytest.mark.parametrize("shape", [(9, 14), (6, 7, 10)])
+def test_pack_unpack_extract(shape):
+    A = torch.arange(torch.Size(shape).numel(), dtype=torch.float64).reshape(shape)
+    Ad = A.cuda()
+    for dim in range(len(shape)):
+        for idx in (0, 1, shape[dim] - 1):
+            plane = A.select(dim, idx)
+            buf = torch.empty(plane.numel(), dtype=torch.float64, device="cuda")
+            native.pack_plane(Ad, dim, idx, buf)
+            assert torch.equal(buf.cpu(), plane.reshape(-1))
+            B = torch.zeros_like(Ad)
+            native.unpack_plane(B, dim, idx, buf)
+            assert torch.equal(B.cpu().select(dim, idx), plane)
+            assert float(B.sum()) == float(plane.sum())
+    inner = native.extract_inner(Ad)
+    assert torch.equal(inner.cpu(), igg.inner(A))
+
+
+def test_reduce_max_sum_repeated_calls():
+    for n in (1, 1000, 1 << 20, (1 << 22) + 3):
+        x = torch.rand(n, dtype=torch.float64, device="cuda") - 0.25
+        for _ in range(2):   # scratch is reused: second call must be right too
+            out = native.reduce_max_sum(x).cpu()
+            assert float(out[0]) == float(x.max())
+            assert abs(float(out[1]) - float(x.sum())) <= 1e-9 * max(1.0, abs(float(x.sum())))
+
+
+def test_colormap_matches_numpy_lut():
+    from rocm_mpi_b200.utils import output
+    f = torch.rand(37, 53, dtype=torch.float64)
+    want = output.colorize(f, 0.0, 1.0)
+    got = output.colorize(f.cuda(), 0.0, 1.0)
+    assert (want == got).all()
+
+
+def test_smoke_entry_point():
+    import __graft_entry__ as ge
+    ge.smoke()

@@ -1,0 +1,42 @@
+"""The native library loads without a GPU and its C++ CPU restatement equals the PyTorch statement."""
+import ctypes
+
+import torch
+
+from rocm_mpi_b200.ops import native, reference as ref
+
+
+def test_library_loads_and_reports_version():
+    lib = native.require()
+    assert lib.igg_version() >= 100
+    assert native.launch_count() >= 0
+
+
+def test_struct_layouts_match_header():
+    assert ctypes.sizeof(native.Push2D) == 9 * 8 * 4 + 16
+    assert ctypes.sizeof(native.Push3D) == 27 * 8 * 4 + 16
+    assert ctypes.sizeof(native.HaloXfer) == 16 + 4 * 12
+    assert ctypes.sizeof(native.HaloSync) == 27 * 8 + 24
+
+
+def test_cpu_step_bit_exact_vs_torch():
+    torch.manual_seed(1)
+    T = torch.rand(37, 52, dtype=torch.float64)
+    Cp = torch.rand(37, 52, dtype=torch.float64) + 0.5
+    want = T.clone()
+    ref.perf_step(want, T, Cp, 1.3, 1e-3, 2.0, 3.0)
+    got = T.clone()
+    native.cpu_diffusion2d_step(got, T, Cp, 1.3, 1e-3, 2.0, 3.0)
+    assert torch.equal(got, want)
+
+
+def test_cpu_run_matches_oracle():
+    T_ref, dt = ref.oracle_2d(62, 48, 25, "perf")
+    dx, dy = 10.0 / 62, 10.0 / 48
+    xs = torch.arange(62, dtype=torch.float64) * dx
+    ys = torch.arange(48, dtype=torch.float64) * dy
+    T = ref.gaussian_ic(xs, ys, dx, dy, 10.0, 10.0)
+    T2 = T.clone()
+    Cp = torch.ones_like(T)
+    native.cpu_diffusion2d_run(T, T2, Cp, 1.0, dt, 1.0 / dx, 1.0 / dy, 25)
+    assert torch.equal(T, T_ref)
