@@ -29,11 +29,14 @@ using namespace igg;
 constexpr int BX = 32;          // tile rows
 constexpr int BY = 128;         // tile columns (contiguous)
 constexpr int STAGES = 3;
-constexpr int TP = BY + 2;      // smem pitch of the T tile (doubles)
-constexpr int T_TILE_BYTES = (BX + 2) * TP * 8;                      // 35360
-constexpr int T_TILE_PAD = (T_TILE_BYTES + 127) / 128 * 128;         // 35456
+// TMA needs the box to start on a 16-byte boundary in global memory, i.e. at an EVEN column for fp64.
+// Tiles start at even columns, so the halo'd box starts two columns to the left (y0-2) and is BY+4
+// wide; the cell (x, y) of a tile sits at smem row x-x0+1, column y-y0+2.
+constexpr int TP = BY + 4;      // smem pitch of the T tile (doubles)
+constexpr int T_TILE_BYTES = (BX + 2) * TP * 8;                      // 35904
+constexpr int T_TILE_PAD = (T_TILE_BYTES + 127) / 128 * 128;         // 35968
 constexpr int CP_TILE_BYTES = BX * BY * 8;                           // 32768
-constexpr int STAGE_BYTES = T_TILE_PAD + CP_TILE_BYTES;              // 68224
+constexpr int STAGE_BYTES = T_TILE_PAD + CP_TILE_BYTES;              // 68736
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 64;                // + mbarriers
 
 struct Seg {
@@ -123,7 +126,7 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
         const int s = k % STAGES;
         unsigned char* st = smem + s * STAGE_BYTES;
         mbar_arrive_expect_tx(&full[s], T_TILE_BYTES + CP_TILE_BYTES);
-        tma_load_2d(st, &mapT, &full[s], j * BY - 1, i * BX - 1);
+        tma_load_2d(st, &mapT, &full[s], j * BY - 2, i * BX - 1);
         tma_load_2d(st + T_TILE_PAD, &mapCp, &full[s], j * BY, i * BX);
     };
 
@@ -143,7 +146,8 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
         const int s = k % STAGES;
         mbar_wait(&full[s], (k / STAGES) & 1);
 
-        const double* sT = reinterpret_cast<const double*>(smem + s * STAGE_BYTES) + (rg * RPT) * TP + 2 * cp;
+        // this thread's two cells sit at smem columns 2cp+2, 2cp+3 (16-byte aligned pair)
+        const double* sT = reinterpret_cast<const double*>(smem + s * STAGE_BYTES) + (rg * RPT) * TP + 2 * cp + 2;
         const double* sC = reinterpret_cast<const double*>(smem + s * STAGE_BYTES + T_TILE_PAD) +
                            (rg * RPT) * BY + 2 * cp;
         const int y = j * BY + 2 * cp;
@@ -153,18 +157,18 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
         const bool vy0 = (y >= 1) && (y <= p.ny - 2);
         const bool vy1 = (y + 1 <= p.ny - 2);
 
-        double2 a0 = *reinterpret_cast<const double2*>(sT);
-        double2 a1 = *reinterpret_cast<const double2*>(sT + 2);
-        double2 b0 = *reinterpret_cast<const double2*>(sT + TP);
-        double2 b1 = *reinterpret_cast<const double2*>(sT + TP + 2);
+        // 3-row register window over x: a = row x-1, b = row x, c = row x+1 (centre pairs)
+        double2 a = *reinterpret_cast<const double2*>(sT);
+        double2 b = *reinterpret_cast<const double2*>(sT + TP);
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
-            const double2 c0 = *reinterpret_cast<const double2*>(sT + (r + 2) * TP);
-            const double2 c1 = *reinterpret_cast<const double2*>(sT + (r + 2) * TP + 2);
+            const double2 c = *reinterpret_cast<const double2*>(sT + (r + 2) * TP);
+            const double bl = sT[(r + 1) * TP - 1];
+            const double br = sT[(r + 1) * TP + 2];
             const double2 cc = *reinterpret_cast<const double2*>(sC + r * BY);
             const int x = xb + r;
-            const double vA = update_cell(b0.y, a0.y, c0.y, b0.x, b1.x, cc.x, lam, dt, _dx, _dy);
-            const double vB = update_cell(b1.x, a1.x, c1.x, b0.y, b1.y, cc.y, lam, dt, _dx, _dy);
+            const double vA = update_cell(b.x, a.x, c.x, bl, b.y, cc.x, lam, dt, _dx, _dy);
+            const double vB = update_cell(b.y, a.y, c.y, b.x, br, cc.y, lam, dt, _dx, _dy);
             const bool vx = (x >= 1) && (x <= p.nx - 2);
             bool wA = vx && vy0, wB = vx && vy1;
             if (p.mode != 0) {
@@ -183,7 +187,8 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
                 if (wA) push_cell_2d(p.push, p.nx, p.ny, x, y, vA);
                 if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
             }
-            a0 = b0; a1 = b1; b0 = c0; b1 = c1;
+            a = b;
+            b = c;
         }
         __syncthreads();   // stage s may be refilled; all remote stores of this tile were issued
         if (edge_tile && tid == 0)
@@ -330,7 +335,7 @@ extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* C
         }
         CUtensorMap mT, mC;
         const uint64_t dims[2] = {(uint64_t)ny, (uint64_t)nx};
-        const uint32_t boxT[2] = {BY + 2, BX + 2};
+        const uint32_t boxT[2] = {TP, BX + 2};
         const uint32_t boxC[2] = {BY, BX};
         int rc = igg::get_tensor_map_f64(T, 2, dims, boxT, &mT);
         if (rc) return rc;

@@ -5,7 +5,7 @@
 // the boundary frame are scheduled first, edge cells are pushed to the up-to-26 neighbours through
 // peer pointers, modes 0/1/2 = all / frame / inside-the-frame.
 //
-//  * variant 1: persistent kernel, 3-D TMA boxes (8 x 8 x 64 cells + halo) through a 3-stage
+//  * variant 1: persistent kernel, 3-D TMA boxes (8 x 8 x 64 cells + halo) through a 2-stage
 //    mbarrier ring, computed from shared memory;
 //  * variant 0: direct global loads, marching along x with a register window.
 // Layout: T[ix][iy][iz], iz contiguous.
@@ -17,15 +17,15 @@ namespace {
 using namespace igg;
 
 constexpr int TX = 8, TY = 8, TZ = 64;       // tile cells
-constexpr int STAGES3 = 3;
-constexpr int PZ = TZ + 2, PY = TY + 2, PX = TX + 2;
-constexpr int T3_BYTES = PX * PY * PZ * 8;                        // 52800
-constexpr int T3_PAD = (T3_BYTES + 127) / 128 * 128;              // 52864
+// The TMA box must start on a 16-byte boundary (even z for fp64): it starts at z0-2 and is TZ+4 wide,
+// so cell (x,y,z) of a tile sits at smem [(x-x0+1)*PY + (y-y0+1)]*PZ + (z-z0+2).
+constexpr int PZ = TZ + 4, PY = TY + 2, PX = TX + 2;
+constexpr int T3_BYTES = PX * PY * PZ * 8;                        // 54400
+constexpr int T3_PAD = (T3_BYTES + 127) / 128 * 128;              // 54400
 constexpr int C3_BYTES = TX * TY * TZ * 8;                        // 32768
-constexpr int STAGE3_BYTES = T3_PAD + C3_BYTES;                   // 85632
-constexpr int SMEM3_BYTES = STAGES3 * STAGE3_BYTES + 64;          // 256960 > 227 KB -> use 2 stages
-constexpr int STAGES3_USED = 2;
-constexpr int SMEM3_USED = STAGES3_USED * STAGE3_BYTES + 64;      // 171328
+constexpr int STAGE3_BYTES = T3_PAD + C3_BYTES;                   // 87168
+constexpr int STAGES3_USED = 2;                                   // 3 stages would exceed 227 KB
+constexpr int SMEM3_USED = STAGES3_USED * STAGE3_BYTES + 64;      // 174400
 
 struct Seg3 {
     int i0, j0, k0, ni, nj, nk, start;
@@ -121,7 +121,7 @@ diff3d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
         const int s = q % STAGES3_USED;
         unsigned char* st = smem + s * STAGE3_BYTES;
         mbar_arrive_expect_tx(&full[s], T3_BYTES + C3_BYTES);
-        tma_load_3d(st, &mapT, &full[s], k * TZ - 1, j * TY - 1, i * TX - 1);
+        tma_load_3d(st, &mapT, &full[s], k * TZ - 2, j * TY - 1, i * TX - 1);
         tma_load_3d(st + T3_PAD, &mapCp, &full[s], k * TZ, j * TY, i * TX);
     };
     if (tid == 0)
@@ -138,29 +138,24 @@ diff3d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
         bool lo[3], hi[3];
         flags_of(i, j, k, lo, hi);
         const bool edge_tile = p.has_push && (lo[0] || lo[1] || lo[2] || hi[0] || hi[1] || hi[2]);
-        // smem cell (x,y,z) of the tile -> [(x+1)*PY + (y+1)]*PZ + (z+1); this thread: z = 2*zp, 2*zp+1
-        const double* sT = reinterpret_cast<const double*>(smem + s * STAGE3_BYTES) + (size_t)(yy + 1) * PZ + 2 * zp;
+        // this thread: y row yy, z cells 2*zp, 2*zp+1 -> smem columns 2*zp+2, 2*zp+3 (aligned pair)
+        const double* sT = reinterpret_cast<const double*>(smem + s * STAGE3_BYTES) + (size_t)(yy + 1) * PZ + 2 * zp + 2;
         const double* sC = reinterpret_cast<const double*>(smem + s * STAGE3_BYTES + T3_PAD) + (size_t)yy * TZ + 2 * zp;
         const int gy = j * TY + yy, gz = k * TZ + 2 * zp;
-        // window over x: centre values of planes x-1, x, x+1 for the two z cells
-        double2 um0 = *reinterpret_cast<const double2*>(sT);               // plane 0 (x-1), cols 2zp,2zp+1
-        double2 um1 = *reinterpret_cast<const double2*>(sT + 2);
-        double2 c0 = *reinterpret_cast<const double2*>(sT + PY * PZ);
-        double2 c1 = *reinterpret_cast<const double2*>(sT + PY * PZ + 2);
+        // window over x: centre pairs of planes x-1 (um), x (c), x+1 (d)
+        double2 um = *reinterpret_cast<const double2*>(sT);
+        double2 c = *reinterpret_cast<const double2*>(sT + PY * PZ);
 #pragma unroll
         for (int r = 0; r < TX; ++r) {
             const double* pl = sT + (size_t)(r + 1) * PY * PZ;            // centre plane
-            const double2 d0 = *reinterpret_cast<const double2*>(pl + PY * PZ);
-            const double2 d1 = *reinterpret_cast<const double2*>(pl + PY * PZ + 2);
-            const double2 ym0 = *reinterpret_cast<const double2*>(pl - PZ);
-            const double2 ym1 = *reinterpret_cast<const double2*>(pl - PZ + 2);
-            const double2 yp0 = *reinterpret_cast<const double2*>(pl + PZ);
-            const double2 yp1 = *reinterpret_cast<const double2*>(pl + PZ + 2);
+            const double2 d = *reinterpret_cast<const double2*>(pl + PY * PZ);
+            const double2 ym = *reinterpret_cast<const double2*>(pl - PZ);
+            const double2 yp = *reinterpret_cast<const double2*>(pl + PZ);
+            const double zl = pl[-1], zr = pl[2];
             const double2 cc = *reinterpret_cast<const double2*>(sC + (size_t)r * TY * TZ);
             const int gx = i * TX + r;
-            // cell A: z = gz   -> centre c0.y, z-1 = c0.x, z+1 = c1.x ; cell B: z = gz+1 -> centre c1.x
-            const double vA = update_cell3(c0.y, um0.y, d0.y, ym0.y, yp0.y, c0.x, c1.x, cc.x, p);
-            const double vB = update_cell3(c1.x, um1.x, d1.x, ym1.x, yp1.x, c0.y, c1.y, cc.y, p);
+            const double vA = update_cell3(c.x, um.x, d.x, ym.x, yp.x, zl, c.y, cc.x, p);
+            const double vB = update_cell3(c.y, um.y, d.y, ym.y, yp.y, c.x, zr, cc.y, p);
             const bool wA = writes(p, gx, gy, gz), wB = writes(p, gx, gy, gz + 1);
             double* out = p.T2 + ((size_t)gx * p.ny + gy) * p.nz + gz;
             if (wA && wB) {
@@ -173,7 +168,8 @@ diff3d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
                 if (wA) push_cell_3d(p.push, p.nx, p.ny, p.nz, gx, gy, gz, vA);
                 if (wB) push_cell_3d(p.push, p.nx, p.ny, p.nz, gx, gy, gz + 1, vB);
             }
-            um0 = c0; um1 = c1; c0 = d0; c1 = d1;
+            um = c;
+            c = d;
         }
         __syncthreads();
         if (edge_tile && tid == 0) signal_edges_3d(p.push, p.edge_tiles, lo, hi);
