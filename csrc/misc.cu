@@ -1,5 +1,7 @@
 // Small device-side utilities: initial condition, plane pack/unpack, interior extraction,
 // max/sum reduction, colour mapping.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -235,3 +237,85 @@ int igg_colormap(const double* field, size_t n, double vmin, double vmax, const 
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// igg_reduce_max_sum_static -- the same max/sum reduction for callers that must not allocate.
+//
+// Who this is for: code that wants the diagnostic (`max(T)`, `sum(T)`) but has no device memory to give
+// and is not allowed to get any -- a monitoring hook that runs after the application has claimed the
+// whole GPU for its fields, a host program whose memory policy reserves all allocation for its own
+// pool, or a time loop that cannot afford the device-wide stall a cudaMalloc/cudaFree causes.  For
+// them the scratch of igg_reduce_max_sum (block partials + ticket) lives in the array below, inside
+// the library image: every GPU that loads the library carries these 16,640 bytes until the process
+// ends, whether or not this entry point is ever called.
+//
+// Contract
+//   * n may not exceed IGG_REDUCE_STATIC_MAX_N (2^29 values = 4 GiB of fp64, twice the 16384^2
+//     flagship field).  The array has room for 1024 block partials and the launch uses at most that
+//     many blocks of 256 threads, so the limit keeps the values folded by one thread -- and with them
+//     the run time and the rounding-error growth of a partial sum -- to a few thousand.  Larger n is
+//     refused with an error message; reduce it in pieces or use igg_reduce_max_sum with your own scratch.
+//   * The first call on each device resolves the device address of the array (cudaGetSymbolAddress,
+//     with that device current).  It is host-side set-up work, so make that first call during
+//     start-up, before any stream capture begins.
+//   * No cudaMalloc, cudaFree or other allocating routine is called, here or in the kernel.
+//   * ALL calls on one device share the one array and it keeps whatever the previous call left in it.
+//     The only part that has to start from zero, the ticket, is cleared on `stream` ahead of every
+//     launch; the partials are rewritten before they are read.  Because of the sharing, two calls
+//     whose kernels can overlap on the GPU (different streams, or different host threads without
+//     ordering between them) race on the partials and the ticket: keep calls on one device ordered.
+//   * Inputs and outputs are the caller's, exactly as for igg_reduce_max_sum.
+// =====================================================================================================
+namespace {
+constexpr size_t STATIC_SCRATCH_BYTES = (sizeof(RedScratch) + 255) / 256 * 256;   // 16,640
+static_assert(STATIC_SCRATCH_BYTES == 16640, "stated size of the built-in scratch");
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_reduce_static_scratch[STATIC_SCRATCH_BYTES];
+
+namespace {
+// Device address of g_reduce_static_scratch per device.  In host code the symbol's own name is only a
+// handle for the runtime, never something a kernel may dereference -- hence cudaGetSymbolAddress.
+std::mutex g_static_mu;
+void* g_static_ptr[64] = {nullptr};
+
+int static_scratch_for_current_device(void** out) {
+    int dev = -1;
+    IGG_CUDA_OK(cudaGetDevice(&dev));
+    IGG_REQUIRE(dev >= 0 && dev < 64, "igg_reduce_max_sum_static: device ordinal %d is out of range", dev);
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (g_static_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_reduce_static_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            igg::set_error("igg_reduce_max_sum_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                           cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : IGG_ERR_INVALID;
+        }
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+extern "C" int igg_reduce_max_sum_static(const double* x, size_t n, double* out, void* stream) {
+    IGG_REQUIRE(x && out && n > 0, "igg_reduce_max_sum_static: bad arguments");
+    if (n > (size_t)IGG_REDUCE_STATIC_MAX_N) {
+        igg::set_error("igg_reduce_max_sum_static: n = %zu exceeds the built-in scratch limit of %zu values "
+                       "(IGG_REDUCE_STATIC_MAX_N); split the input or call igg_reduce_max_sum with your own scratch",
+                       n, (size_t)IGG_REDUCE_STATIC_MAX_N);
+        return IGG_ERR_UNSUPPORTED;
+    }
+    void* scratch = nullptr;
+    int rc = static_scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array still holds the previous call's state: the ticket is the one field that must be zero
+    IGG_CUDA_OK(cudaMemsetAsync(scratch, 0, 16, st));
+    int blocks = grid_for(n, RED_THREADS, 4);
+    if (blocks > RED_MAX_BLOCKS) blocks = RED_MAX_BLOCKS;
+    reduce_max_sum_kernel<<<blocks, RED_THREADS, 0, st>>>(x, n, (RedScratch*)scratch, out);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}

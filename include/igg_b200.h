@@ -163,6 +163,20 @@ int igg_wait_value(uint64_t* my_flag, uint64_t value, uint64_t* err_word, void* 
  * must not overlap on the GPU.  `out`: two device doubles {max, sum}. */
 size_t igg_reduce_scratch_bytes(size_t n);
 int igg_reduce_max_sum(const double* x, size_t n, void* scratch, double* out, void* stream);
+/* The same reduction for callers that cannot allocate device memory (no counterpart in the
+ * reference: it never reduces on the device without allocating).  Meant for hooks that run after the
+ * application has taken the whole GPU for its fields, for hosts whose memory policy keeps allocation
+ * to their own pool, and for time loops that cannot take the device-wide stall of cudaMalloc/cudaFree.
+ * The scratch is a 16,640-byte array built into the library (held by every GPU that loads it, until
+ * exit); inputs and outputs are still yours.
+ *   - n <= IGG_REDUCE_STATIC_MAX_N, else IGG_ERR_UNSUPPORTED and a message naming the limit;
+ *   - no cudaMalloc/cudaFree or allocating library call is made;
+ *   - the first call on each device looks up the array's device address (host-side set-up): make it
+ *     during start-up, before any stream capture;
+ *   - all calls on a device share the array and it keeps the last call's contents (the ticket is
+ *     re-zeroed on `stream` before each launch); calls that can overlap on the GPU race -- order them. */
+#define IGG_REDUCE_STATIC_MAX_N (((size_t)1) << 29)
+int igg_reduce_max_sum_static(const double* x, size_t n, double* out, void* stream);
 /* field -> RGB8 through a 256x3 look-up table (reference scripts/diffusion_2D_ap.jl:47 heatmap) */
 int igg_colormap(const double* field, size_t n, double vmin, double vmax, const uint8_t* lut_dev,
                  uint8_t* rgb, void* stream);
