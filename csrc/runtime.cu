@@ -1,5 +1,6 @@
 // Library runtime: error state, launch accounting, device queries, tensor-map cache.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -52,6 +53,17 @@ static EncodeTiledFn encode_fn() {
             fn = (EncodeTiledFn)p;
     });
     return fn;
+}
+
+// L2 fetch granularity of TMA loads (IGG_L2_PROMO = 0 none, 1 64 B, 2 128 B, 3 256 B)
+static CUtensorMapL2promotion l2_promotion() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("IGG_L2_PROMO");
+        v = e ? atoi(e) : 2;
+        if (v < 0 || v > 3) v = 2;
+    }
+    return (CUtensorMapL2promotion)v;
 }
 
 struct MapKey {
@@ -112,7 +124,7 @@ int get_tensor_map_f64(const void* base, int rank, const uint64_t* dims, const u
     CUtensorMap m;
     CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, (cuuint32_t)rank, const_cast<void*>(base), gdims,
                     gstrides, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    l2_promotion(), CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
         return IGG_ERR_UNSUPPORTED;

@@ -18,6 +18,7 @@
 //    it is the "recompiled baseline" flavour and the fallback for odd ny.
 //
 // Layout: T[ix][iy], iy contiguous.  "x" rows are strided, "y" columns contiguous.
+#include <stdlib.h>
 #include <string.h>
 
 #include "push.cuh"
@@ -28,7 +29,6 @@ using namespace igg;
 
 constexpr int BX = 32;          // tile rows
 constexpr int BY = 128;         // tile columns (contiguous)
-constexpr int STAGES = 3;
 // TMA needs the box to start on a 16-byte boundary in global memory, i.e. at an EVEN column for fp64.
 // Tiles start at even columns, so the halo'd box starts two columns to the left (y0-2) and is BY+4
 // wide; the cell (x, y) of a tile sits at smem row x-x0+1, column y-y0+2.
@@ -36,11 +36,21 @@ constexpr int TP = BY + 4;      // smem pitch of the T tile (doubles)
 constexpr int T_TILE_BYTES = (BX + 2) * TP * 8;                      // 35904
 constexpr int T_TILE_PAD = (T_TILE_BYTES + 127) / 128 * 128;         // 35968
 constexpr int CP_TILE_BYTES = BX * BY * 8;                           // 32768
-constexpr int STAGE_BYTES = T_TILE_PAD + CP_TILE_BYTES;              // 68736
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 64;                // + mbarriers
+// a pipeline stage holds the T tile and, when Cp is staged by TMA too, the Cp tile
+constexpr int stage_bytes(bool cp_tma) { return T_TILE_PAD + (cp_tma ? CP_TILE_BYTES : 0); }
+constexpr int smem_bytes(int stages, bool cp_tma) { return stages * stage_bytes(cp_tma) + 64; }   // + mbarriers
+
+// same layout as the scratch of igg_reduce_max_sum (csrc/misc.cu)
+struct DiagScratch {
+    unsigned int ticket;
+    unsigned int pad[3];
+    double pmax[1024];
+    double psum[1024];
+};
 
 struct Seg {
     int i0, j0, w, h, start;    // tiles [i0,i0+h) x [j0,j0+w); `start` = linear id of its first tile
+    int band;                   // > 0: walk the segment in vertical bands of `band` tile columns
 };
 struct TileSet {
     Seg s[5];
@@ -54,10 +64,13 @@ struct Params {
     int nx, ny;
     double lam, dt, _dx, _dy;
     const double* dev_params;   // optional {lam, dt, _dx, _dy} in device memory
+    double* diag_out;           // optional {max, sum} of the written cells
+    struct DiagScratch* diag;   // block partials + ticket for diag_out
     int mode, bwx, bwy;
     int i_hi, j_hi;             // tile row/column that contains x==nx-2 / y==ny-2
     TileSet ts;
     int has_push;
+    int l2_hints;               // 0 none, 1 Cp evict-first, 2 Cp evict-first + T evict-last
     int edge_tiles[9];
     igg_push2d push;
 };
@@ -71,8 +84,19 @@ __device__ __forceinline__ void tile_of(const TileSet& ts, int t, int& i, int& j
             const Seg& s = ts.s[k];
             const int r = t - s.start;
             if (r >= 0 && r < s.w * s.h) {
-                i = s.i0 + r / s.w;
-                j = s.j0 + r % s.w;
+                if (s.band > 0) {
+                    // banded order: consecutive tile ids sweep `band` columns, then drop one tile row, so
+                    // the CTAs resident at one time hold vertical AND horizontal neighbours (halo rows
+                    // and columns are fetched from DRAM once and shared through L2)
+                    const int per_band = s.band * s.h;
+                    const int b = r / per_band, rr = r - b * per_band;
+                    const int jw = min(s.band, s.w - b * s.band);
+                    i = s.i0 + rr / jw;
+                    j = s.j0 + b * s.band + rr % jw;
+                } else {
+                    i = s.i0 + r / s.w;
+                    j = s.j0 + r % s.w;
+                }
             }
         }
     }
@@ -96,11 +120,14 @@ __device__ __forceinline__ bool in_frame(const Params& p, int x, int y) {
 // ------------------------------------------------------------------------------------------------
 // variant 1: persistent, TMA + mbarrier pipeline
 // ------------------------------------------------------------------------------------------------
-template <int RPT>   // rows per thread
-__global__ void __launch_bounds__((BY / 2) * (BX / RPT), 1)
+// RPT rows per thread; STAGES ring depth; CP_TMA: Cp tile staged by TMA (else read straight from global
+// into registers before the stage wait); MINB resident CTAs per SM the register budget is sized for.
+template <int RPT, int STAGES, bool CP_TMA, int MINB>
+__global__ void __launch_bounds__((BY / 2) * (BX / RPT), MINB)
 diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapCp,
                   const __grid_constant__ Params p) {
     extern __shared__ __align__(128) unsigned char smem[];
+    constexpr int STAGE_BYTES = stage_bytes(CP_TMA);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
     const int tid = threadIdx.x;
     const int ntiles = p.ts.ntiles;
@@ -125,9 +152,15 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
         }
         const int s = k % STAGES;
         unsigned char* st = smem + s * STAGE_BYTES;
-        mbar_arrive_expect_tx(&full[s], T_TILE_BYTES + CP_TILE_BYTES);
-        tma_load_2d(st, &mapT, &full[s], j * BY - 2, i * BX - 1);
-        tma_load_2d(st + T_TILE_PAD, &mapCp, &full[s], j * BY, i * BX);
+        mbar_arrive_expect_tx(&full[s], T_TILE_BYTES + (CP_TMA ? CP_TILE_BYTES : 0));
+        if (p.l2_hints) {
+            tma_load_2d_hint(st, &mapT, &full[s], j * BY - 2, i * BX - 1,
+                             p.l2_hints == 2 ? L2_EVICT_LAST : L2_EVICT_NORMAL);
+            if (CP_TMA) tma_load_2d_hint(st + T_TILE_PAD, &mapCp, &full[s], j * BY, i * BX, L2_EVICT_FIRST);
+        } else {
+            tma_load_2d(st, &mapT, &full[s], j * BY - 2, i * BX - 1);
+            if (CP_TMA) tma_load_2d(st + T_TILE_PAD, &mapCp, &full[s], j * BY, i * BX);
+        }
     };
 
     if (tid == 0) {
@@ -139,11 +172,26 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
     const double lam = p.dev_params ? p.dev_params[0] : p.lam, dt = p.dev_params ? p.dev_params[1] : p.dt;
     const double _dx = p.dev_params ? p.dev_params[2] : p._dx, _dy = p.dev_params ? p.dev_params[3] : p._dy;
 
+    const bool diag = p.diag_out != nullptr;
+    double dmax = -INFINITY, dsum = 0.0;
+
     for (int k = 0; k < n_my; ++k) {
         if (tid == 0 && k + STAGES - 1 < n_my) issue(k + STAGES - 1);
         int i, j;
         tile_of(p.ts, first + k * gridDim.x, i, j);
         const int s = k % STAGES;
+        // Cp without TMA: issue this thread's RPT 16-byte loads now, so their latency overlaps the wait
+        double2 cpr[RPT];
+        if (!CP_TMA) {
+            const int yq = j * BY + 2 * cp;
+#pragma unroll
+            for (int r = 0; r < RPT; ++r) {
+                int xq = i * BX + rg * RPT + r;
+                xq = xq < p.nx ? xq : p.nx - 1;                       // clamp: masked cells are never stored
+                const int yc = yq + 1 < p.ny ? yq : p.ny - 2;         // ny is even, so yq is even and this stays aligned
+                cpr[r] = __ldg(reinterpret_cast<const double2*>(p.Cp + (size_t)xq * p.ny + yc));
+            }
+        }
         mbar_wait(&full[s], (k / STAGES) & 1);
 
         // this thread's two cells sit at smem columns 2cp+2, 2cp+3 (16-byte aligned pair)
@@ -165,7 +213,7 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
             const double2 c = *reinterpret_cast<const double2*>(sT + (r + 2) * TP);
             const double bl = sT[(r + 1) * TP - 1];
             const double br = sT[(r + 1) * TP + 2];
-            const double2 cc = *reinterpret_cast<const double2*>(sC + r * BY);
+            const double2 cc = CP_TMA ? *reinterpret_cast<const double2*>(sC + r * BY) : cpr[r];
             const int x = xb + r;
             const double vA = update_cell(b.x, a.x, c.x, bl, b.y, cc.x, lam, dt, _dx, _dy);
             const double vB = update_cell(b.y, a.y, c.y, b.x, br, cc.y, lam, dt, _dx, _dy);
@@ -187,12 +235,65 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
                 if (wA) push_cell_2d(p.push, p.nx, p.ny, x, y, vA);
                 if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
             }
+            if (diag) {
+                if (wA) { dmax = fmax(dmax, vA); dsum += vA; }
+                if (wB) { dmax = fmax(dmax, vB); dsum += vB; }
+            }
             a = b;
             b = c;
         }
         __syncthreads();   // stage s may be refilled; all remote stores of this tile were issued
         if (edge_tile && tid == 0)
             signal_edges_2d(p.push, p.edge_tiles, i == 0, i == p.i_hi, j == 0, j == p.j_hi);
+    }
+
+    // fused diagnostic: CTA partial -> scratch, last CTA (ticket) folds all partials in a fixed order
+    if (diag) {
+        constexpr int NW = (BY / 2) * (BX / RPT) / 32;
+        double* red = reinterpret_cast<double*>(smem);          // all stages have been consumed
+        __shared__ bool is_last;
+        auto block_fold = [&](double& mx, double& sm) {
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                sm += __shfl_xor_sync(0xffffffffu, sm, off);
+            }
+            if ((tid & 31) == 0) { red[tid >> 5] = mx; red[32 + (tid >> 5)] = sm; }
+            __syncthreads();
+            if (tid < 32) {
+                mx = tid < NW ? red[tid] : -INFINITY;
+                sm = tid < NW ? red[32 + tid] : 0.0;
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) {
+                    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                    sm += __shfl_xor_sync(0xffffffffu, sm, off);
+                }
+            }
+            __syncthreads();
+        };
+        block_fold(dmax, dsum);
+        if (tid == 0) {
+            p.diag->pmax[blockIdx.x] = dmax;
+            p.diag->psum[blockIdx.x] = dsum;
+            __threadfence();
+            is_last = atomicAdd(&p.diag->ticket, 1u) == gridDim.x - 1;
+        }
+        __syncthreads();
+        if (is_last) {
+            __threadfence();
+            dmax = -INFINITY;
+            dsum = 0.0;
+            for (unsigned int b2 = tid; b2 < gridDim.x; b2 += blockDim.x) {
+                dmax = fmax(dmax, p.diag->pmax[b2]);
+                dsum += p.diag->psum[b2];
+            }
+            block_fold(dmax, dsum);
+            if (tid == 0) {
+                p.diag_out[0] = dmax;
+                p.diag_out[1] = dsum;
+                p.diag->ticket = 0;
+            }
+        }
     }
 }
 
@@ -250,9 +351,10 @@ __global__ void __launch_bounds__(256) diff2d_direct_kernel(const __grid_constan
 // ------------------------------------------------------------------------------------------------
 // host: tile lists
 // ------------------------------------------------------------------------------------------------
-static void add_seg(TileSet& ts, int i0, int i1, int j0, int j1) {   // inclusive tile ranges
+static void add_seg(TileSet& ts, int i0, int i1, int j0, int j1, int band = 0) {   // inclusive tile ranges
     if (i1 < i0 || j1 < j0) return;
     Seg& s = ts.s[ts.nseg++];
+    s.band = band;
     s.i0 = i0;
     s.j0 = j0;
     s.h = i1 - i0 + 1;
@@ -261,14 +363,43 @@ static void add_seg(TileSet& ts, int i0, int i1, int j0, int j1) {   // inclusiv
     ts.ntiles += s.w * s.h;
 }
 
+static int tma_config() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("IGG_TMA_CFG");
+        v = e ? atoi(e) : 4;
+    }
+    return v;
+}
+
+static int l2_hints() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("IGG_L2_HINTS");
+        v = e ? atoi(e) : 0;
+    }
+    return v;
+}
+
+static int tile_band() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("IGG_TILE_BAND");
+        v = e ? atoi(e) : 16;
+        if (v < 0) v = 0;
+    }
+    return v;
+}
+
 static void build_tiles(TileSet& ts, int nx, int ny, int mode, int bwx, int bwy) {
     ts.nseg = 0;
     ts.ntiles = 0;
+    const int band = tile_band();
     const int nti = (nx - 2) / BX + 1, ntj = (ny - 2) / BY + 1;
     if (mode == 2) {
         const int x0 = 1 + bwx, x1 = nx - 2 - bwx, y0 = 1 + bwy, y1 = ny - 2 - bwy;
         if (x1 < x0 || y1 < y0) return;
-        add_seg(ts, x0 / BX, x1 / BX, y0 / BY, y1 / BY);
+        add_seg(ts, x0 / BX, x1 / BX, y0 / BY, y1 / BY, band);
         return;
     }
     // tile rows / columns that intersect the boundary frame
@@ -277,7 +408,7 @@ static void build_tiles(TileSet& ts, int nx, int ny, int mode, int bwx, int bwy)
     int b0 = (bwy < ny - 2 ? bwy : ny - 2) / BY;
     int b1 = (ny - 1 - bwy > 1 ? ny - 1 - bwy : 1) / BY;
     if (a1 <= a0) {  // bands meet: everything is frame
-        add_seg(ts, 0, nti - 1, 0, ntj - 1);
+        add_seg(ts, 0, nti - 1, 0, ntj - 1, band);
         return;
     }
     add_seg(ts, 0, a0, 0, ntj - 1);
@@ -288,15 +419,14 @@ static void build_tiles(TileSet& ts, int nx, int ny, int mode, int bwx, int bwy)
     }
     add_seg(ts, a0 + 1, a1 - 1, 0, b0);
     add_seg(ts, a0 + 1, a1 - 1, b1, ntj - 1);
-    if (mode == 0) add_seg(ts, a0 + 1, a1 - 1, b0 + 1, b1 - 1);
+    if (mode == 0) add_seg(ts, a0 + 1, a1 - 1, b0 + 1, b1 - 1, band);
 }
 
-static bool g_attr_set[64] = {false};   // per device: opt-in dynamic shared memory size applied
 
 }  // namespace
 
 extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
-                                    double dt, double _dx, double _dy, const double* dev_params, int mode, int bwx,
+                                    double dt, double _dx, double _dy, const igg_step_opts* opts, int mode, int bwx,
                                     int bwy, int variant, const igg_push2d* push, void* stream) {
     IGG_REQUIRE(T && T2 && Cp, "igg_diffusion2d_step: null field pointer");
     IGG_REQUIRE(nx >= 3 && ny >= 3, "igg_diffusion2d_step: need nx, ny >= 3 (got %d x %d)", nx, ny);
@@ -309,13 +439,18 @@ extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* C
     Params p;
     p.T = T; p.T2 = T2; p.Cp = Cp; p.nx = nx; p.ny = ny;
     p.lam = lam; p.dt = dt; p._dx = _dx; p._dy = _dy;
-    p.dev_params = dev_params;
+    p.dev_params = opts ? opts->dev_params : nullptr;
+    p.diag_out = opts ? opts->diag_out : nullptr;
+    p.diag = opts ? (DiagScratch*)opts->diag_scratch : nullptr;
+    IGG_REQUIRE(!p.diag_out || (p.diag && variant == 1),
+                "igg_diffusion2d_step: diag_out needs diag_scratch and the TMA variant (variant 1)");
     p.mode = mode; p.bwx = bwx; p.bwy = bwy;
     p.i_hi = (nx - 2) / BX;
     p.j_hi = (ny - 2) / BY;
     build_tiles(p.ts, nx, ny, mode, bwx, bwy);
     if (p.ts.ntiles == 0) return 0;
     p.has_push = push ? 1 : 0;
+    p.l2_hints = l2_hints();
     const int nti = p.i_hi + 1, ntj = p.j_hi + 1;
     for (int sx = -1; sx <= 1; ++sx)
         for (int sy = -1; sy <= 1; ++sy)
@@ -341,16 +476,31 @@ extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* C
         if (rc) return rc;
         rc = igg::get_tensor_map_f64(Cp, 2, dims, boxC, &mC);
         if (rc) return rc;
-        constexpr int RPT = 4;
-        auto kern = diff2d_tma_kernel<RPT>;
         int dev = 0;
         IGG_CUDA_OK(cudaGetDevice(&dev));
-        if (dev < 0 || dev >= 64 || !g_attr_set[dev]) {
-            IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-            if (dev >= 0 && dev < 64) g_attr_set[dev] = true;
+        const int grid_cap = igg::sm_count();
+#define IGG_LAUNCH_TMA(RPT_, ST_, CPT_, MINB_)                                                                  \
+        do {                                                                                                        \
+            auto kern = diff2d_tma_kernel<RPT_, ST_, CPT_, MINB_>;                                                  \
+            constexpr int SM_ = smem_bytes(ST_, CPT_);                                                              \
+            static bool attr_set[64] = {false};                                                                     \
+            if (dev < 0 || dev >= 64 || !attr_set[dev]) {                                                           \
+                IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_));          \
+                if (dev >= 0 && dev < 64) attr_set[dev] = true;                                                     \
+            }                                                                                                       \
+            const int cap = grid_cap * MINB_;                                                                       \
+            const int grid = p.ts.ntiles < cap ? p.ts.ntiles : cap;                                                 \
+            kern<<<grid, (BY / 2) * (BX / RPT_), SM_, st>>>(mT, mC, p);                                             \
+        } while (0)
+        switch (tma_config()) {
+            case 1: IGG_LAUNCH_TMA(4, 3, false, 2); break;   // 512 thr, Cp direct, 2 CTA/SM
+            case 2: IGG_LAUNCH_TMA(8, 3, false, 2); break;   // 256 thr, Cp direct, 2 CTA/SM
+            case 3: IGG_LAUNCH_TMA(8, 2, false, 3); break;   // 256 thr, Cp direct, 3 CTA/SM
+            case 4: IGG_LAUNCH_TMA(8, 3, true, 1); break;    // 256 thr, Cp by TMA, 1 CTA/SM
+            case 5: IGG_LAUNCH_TMA(16, 3, true, 1); break;   // 128 thr, Cp by TMA, 1 CTA/SM
+            default: IGG_LAUNCH_TMA(4, 3, true, 1); break;   // 512 thr, Cp by TMA, 1 CTA/SM
         }
-        const int grid = p.ts.ntiles < igg::sm_count() ? p.ts.ntiles : igg::sm_count();
-        kern<<<grid, (BY / 2) * (BX / RPT), SMEM_BYTES, st>>>(mT, mC, p);
+#undef IGG_LAUNCH_TMA
         IGG_LAUNCH_CHECK();
     } else {
         diff2d_direct_kernel<<<p.ts.ntiles, 256, 0, st>>>(p);

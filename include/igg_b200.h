@@ -59,10 +59,20 @@ typedef struct igg_push2d {
     uint64_t epoch;                 /* this step's epoch; halo reads wait for epoch-1            */
 } igg_push2d;
 
-/* `dev_params` (may be NULL): device array {lam, dt, _dx, _dy} that overrides the by-value scalars,
- * so a host control loop can feed per-step parameters through an asynchronous H2D copy. */
+/* Optional extras of a step (pass NULL for none):
+ *   dev_params   device array {lam, dt, _dx, _dy} that overrides the by-value scalars, so a host control
+ *                loop can feed per-step parameters through an asynchronous H2D copy;
+ *   diag_out     device array of two doubles that receives {max, sum} over the cells written by this
+ *                launch (the halo-free interior in mode 0) -- the `maximum(T_v)` diagnostic of reference
+ *                scripts/diffusion_2D_perf_hide.jl:115 computed inside the stencil kernel, no extra pass;
+ *                variant 1 only.  `diag_scratch`: igg_reduce_scratch_bytes(0) bytes, zero-filled once. */
+typedef struct igg_step_opts {
+    const double* dev_params;
+    double* diag_out;
+    void* diag_scratch;
+} igg_step_opts;
 int igg_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
-                         double dt, double _dx, double _dy, const double* dev_params, int mode, int bwx,
+                         double dt, double _dx, double _dy, const igg_step_opts* opts, int mode, int bwx,
                          int bwy, int variant, const igg_push2d* push, void* stream);
 
 /* ---- 2-D diffusion, three-kernel form (reference scripts/diffusion_2D_kp.jl:16-54) ------------ */

@@ -123,16 +123,22 @@ class Diffusion2D:
         self._running = False
 
     # -- stepping ---------------------------------------------------------------------------------
-    def _kernel(self, mode: int, push, dev_params=None) -> None:
+    def _kernel(self, mode: int, push, dev_params=None, diag_out=None) -> None:
         native.diffusion2d_step(self.T2, self.T, self.Cp, self.lam, self.dt, self._dx, self._dy, mode=mode,
-                                b_width=self.b_width, variant=self.variant, push=push, dev_params=dev_params)
+                                b_width=self.b_width, variant=self.variant, push=push, dev_params=dev_params,
+                                diag_out=diag_out)
 
-    def step(self, n: int = 1, dev_params: Optional[torch.Tensor] = None) -> None:
+    def step(self, n: int = 1, dev_params: Optional[torch.Tensor] = None,
+             diag_out: Optional[torch.Tensor] = None) -> None:
+        """Advance ``n`` steps.  ``diag_out`` (fused mode, TMA kernel): device ``[max, sum]`` of the cells
+        updated by the step, computed inside the stencil kernel."""
         if not self._running:
             self.begin()
+        if diag_out is not None and not self.fused_diag:
+            raise ValueError("in-kernel diagnostics need mode='fused' or 'plain' with variant='tma'")
         for _ in range(n):
             if self.mode == "fused":
-                self._kernel(0, self.plan.next(self.T2), dev_params)
+                self._kernel(0, self.plan.next(self.T2), dev_params, diag_out)
                 self.T, self.T2 = self.T2, self.T
             elif self.mode == "hide":
                 main = torch.cuda.current_stream()
@@ -149,25 +155,35 @@ class Diffusion2D:
                 main.wait_event(self._ev_lo)
                 self.T, self.T2 = self.T2, self.T
             else:
-                self._kernel(0, None, dev_params)
+                self._kernel(0, None, dev_params, diag_out)
                 self.T, self.T2 = self.T2, self.T
                 if self.g.nprocs > 1 or any(self.g.periods):
                     update_halo(self.T, transport=self.transport)
             self.steps_done += 1
 
     def step_controlled(self, lam: Optional[float] = None, dt: Optional[float] = None) -> Tuple[float, float]:
-        """One end-to-end step: parameters in through pinned memory, ``(max, sum)`` of the new field out."""
+        """One end-to-end step: parameters in through pinned memory, ``(max, sum)`` of the new field out.
+
+        The diagnostic covers the cells this rank updated (its halo-free interior), i.e. the local part of
+        ``maximum(T_v)`` / ``sum(T_v)`` of the gathered field."""
         p = self._params_pin
         p[0] = self.lam if lam is None else lam
         p[1] = self.dt if dt is None else dt
         p[2] = self._dx
         p[3] = self._dy
         self._params_dev.copy_(p, non_blocking=True)                   # H2D, 32 bytes
-        self.step(1, dev_params=self._params_dev)
-        native.reduce_max_sum(self.T.view(-1), self._diag_dev)
+        if self.fused_diag:
+            self.step(1, dev_params=self._params_dev, diag_out=self._diag_dev)   # diagnostic inside the kernel
+        else:
+            self.step(1, dev_params=self._params_dev)
+            native.reduce_max_sum(native.extract_inner(self.T).view(-1), self._diag_dev)
         self._diag_pin.copy_(self._diag_dev, non_blocking=True)        # D2H, 16 bytes
         torch.cuda.current_stream().synchronize()
         return float(self._diag_pin[0]), float(self._diag_pin[1])
+
+    @property
+    def fused_diag(self) -> bool:
+        return self.variant == "tma" and self.mode in ("fused", "plain")
 
     h2d_bytes_per_step = 32
     d2h_bytes_per_step = 16

@@ -36,6 +36,10 @@ class Push3D(C.Structure):
                 ("my_count", C.c_void_p * 27), ("err_word", C.c_void_p), ("epoch", C.c_uint64)]
 
 
+class StepOpts(C.Structure):
+    _fields_ = [("dev_params", C.c_void_p), ("diag_out", C.c_void_p), ("diag_scratch", C.c_void_p)]
+
+
 class HaloXfer(C.Structure):
     _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("n", C.c_int * 3), ("src_start", C.c_int * 3),
                 ("dst_start", C.c_int * 3), ("extent", C.c_int * 3)]
@@ -61,7 +65,8 @@ def _declare(lib) -> None:
         "igg_last_error": ([], C.c_char_p),
         "igg_device_info": ([C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(sz)], i),
         "igg_launch_count": ([], C.c_ulonglong),
-        "igg_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d, vp, i, i, i, i, C.POINTER(Push2D), vp], i),
+        "igg_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d, C.POINTER(StepOpts), i, i, i, i,
+                                 C.POINTER(Push2D), vp], i),
         "igg_flux2d": ([vp, vp, vp, i, i, d, d, d, vp], i),
         "igg_residual2d": ([vp, vp, vp, vp, i, i, d, d, vp], i),
         "igg_update2d": ([vp, vp, i, i, d, C.POINTER(Push2D), vp], i),
@@ -165,16 +170,26 @@ VARIANTS = {"direct": 0, "tma": 1}
 
 def diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
                      _dy: float, mode: int = 0, b_width: Sequence[int] = (1, 1), variant: str = "tma",
-                     push: Optional[Push2D] = None, dev_params: Optional[torch.Tensor] = None) -> None:
+                     push: Optional[Push2D] = None, dev_params: Optional[torch.Tensor] = None,
+                     diag_out: Optional[torch.Tensor] = None) -> None:
     """``T2 <- step(T)``; see ``igg_diffusion2d_step`` in ``include/igg_b200.h``.
 
-    ``dev_params``: optional device tensor ``[lam, dt, _dx, _dy]`` overriding the scalar arguments."""
+    ``dev_params``: optional device tensor ``[lam, dt, _dx, _dy]`` overriding the scalar arguments.
+    ``diag_out``: optional device tensor of 2 doubles receiving ``[max, sum]`` over the cells written by
+    this launch, computed inside the stencil kernel (TMA variant only)."""
     lib = require()
     nx, ny = T.shape
     if T2.shape != T.shape or Cp.shape != T.shape:
         raise ValueError("T, T2 and Cp must have the same shape")
+    opts = None
+    if dev_params is not None or diag_out is not None:
+        opts = StepOpts()
+        opts.dev_params = _f64(dev_params, "dev_params") if dev_params is not None else None
+        if diag_out is not None:
+            opts.diag_out = _f64(diag_out, "diag_out")
+            opts.diag_scratch = _reduce_scratch(T.device).data_ptr()
     _check(lib.igg_diffusion2d_step(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
-                                    _f64(dev_params, "dev_params") if dev_params is not None else None,
+                                    C.byref(opts) if opts is not None else None,
                                     mode, int(b_width[0]), int(b_width[1]), VARIANTS[variant],
                                     C.byref(push) if push is not None else None, _stream()))
 
@@ -247,6 +262,17 @@ def extract_inner(A, out=None) -> torch.Tensor:
 
 # ---- diagnostics ------------------------------------------------------------------------------------
 _reduce_ws = {}
+_diag_ws = {}
+
+
+def _reduce_scratch(device: torch.device) -> torch.Tensor:
+    """Zero-initialised scratch for the in-kernel diagnostic (one per device, separate from the one used
+    by :func:`reduce_max_sum` so the two kinds of launches may overlap)."""
+    ws = _diag_ws.get(device.index)
+    if ws is None:
+        ws = torch.zeros(int(require().igg_reduce_scratch_bytes(0)), dtype=torch.uint8, device=device)
+        _diag_ws[device.index] = ws
+    return ws
 
 
 def reduce_max_sum(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -186,3 +186,21 @@ def test_colormap_matches_numpy_lut():
 def test_smoke_entry_point():
     import __graft_entry__ as ge
     ge.smoke()
+
+
+def test_in_kernel_diagnostic_matches_torch():
+    for (nx, ny) in ((66, 130), (300, 1026), (1100, 2050)):
+        T, Cp = _fields(nx, ny, 21)
+        T = T - 0.3
+        want = T.clone()
+        ref.perf_step(want, T, Cp, 1.0, 1e-3, 2.0, 3.0)
+        inner = want[1:-1, 1:-1]
+        T2d = T.cuda().clone()
+        out = torch.full((2,), float("nan"), dtype=torch.float64, device="cuda")
+        for rep in range(2):          # the scratch is reused between calls
+            native.diffusion2d_step(T2d, T.cuda(), Cp.cuda(), 1.0, 1e-3, 2.0, 3.0, variant="tma", diag_out=out)
+            got = out.cpu()
+            assert abs(float(got[0]) - float(inner.max())) < 1e-14
+            assert abs(float(got[1]) - float(inner.sum())) <= 1e-10 * abs(float(inner.sum())) + 1e-9
+    with pytest.raises(native.NativeError):
+        native.diffusion2d_step(T2d, T.cuda(), Cp.cuda(), 1.0, 1e-3, 2.0, 3.0, variant="direct", diag_out=out)
