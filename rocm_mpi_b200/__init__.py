@@ -6,6 +6,7 @@ Public surface (what the reference scripts call through ImplicitGlobalGrid, e.g.
 ``init_global_grid  finalize_global_grid  update_halo  gather  nx_g ny_g nz_g  x_g y_g z_g
 tic toc  select_device  hide_communication``
 """
+from .parallel import hide_communication  # noqa: F401
 from .parallel import (PROC_NULL, VirtualGrid, a_eff, coords_g, dims_create, finalize_global_grid,  # noqa: F401
                        gather, gather_interior, global_grid, grid_is_initialized, init_global_grid, inner,
                        nx_g, ny_g, nz_g, ol, select_device, t_eff, tic, toc, update_halo, x_g, y_g, z_g)

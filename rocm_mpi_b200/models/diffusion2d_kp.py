@@ -1,0 +1,111 @@
+"""2-D heat diffusion, kernel-programming variant (``kp``): three explicit kernels per step.
+
+Behavioural counterpart of reference ``scripts/diffusion_2D_kp.jl``: ``Flux!`` (``:16-26``), ``Residual!``
+(``:33-40``), ``Update!`` (``:47-54``), then ``update_halo!(T)`` (``:91``), gather and heat map (``:93-96``).
+The reference blocks the host after every launch (``wait(@roc ...)``, ``:88-90``); here the kernels are
+queued on one stream with no host waits.
+
+Halo handling (``--transport``):
+
+* ``peer`` (default on several GPUs): ``Update!`` itself stores the edge cells into the neighbours' halo
+  cells and releases the step's epoch.  Because the update is in place, two tiny flag kernels bracket the
+  step: wait for the neighbours' previous epoch before ``Flux!`` reads the halo, and a neighbour barrier
+  before ``Update!`` overwrites what the neighbours' ``Flux!`` is still reading.
+* ``nccl`` / ``host``: the three kernels, then ``update_halo(T)`` with pack -> send/recv -> unpack.
+
+Run:  ``torchrun --nproc-per-node 8 -m rocm_mpi_b200.models.diffusion2d_kp --nx 65 --ny 128 --dimx 4 --dimy 2``
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+
+import torch
+
+from ..ops import native
+from ..ops import reference as ref
+from ..parallel import finalize_global_grid, global_grid, update_halo
+from ..parallel.fabric import PushPlan, fabric_zeros, get_fabric
+from ..parallel.halo import default_transport
+from ..utils.config import DiffusionConfig, add_config_args, config_from_args
+from .common import RunResult, initial_condition_2d, log0, setup_2d, visualise_2d
+
+__all__ = ["diffusion2D_kp", "main"]
+
+
+def diffusion2D_kp(cfg: DiffusionConfig = None, finalize: bool = True) -> RunResult:
+    cfg = cfg or DiffusionConfig()
+    s = setup_2d(cfg)
+    g = global_grid()
+    dev, f64 = s.device, torch.float64
+    nx, ny = cfg.nx, cfg.ny
+    on_gpu = dev.type == "cuda"
+    if on_gpu:
+        native.require()
+    _dx, _dy = 1.0 / s.dx, 1.0 / s.dy
+    transport = cfg.transport or default_transport(torch.empty(0, device=dev))
+    comm_needed = g.nprocs > 1 or any(g.periods)
+    fused_push = on_gpu and transport == "peer" and cfg.fused and comm_needed
+    # Array initializations (reference scripts/diffusion_2D_kp.jl:73-78)
+    dTdt = torch.zeros(nx - 2, ny - 2, dtype=f64, device=dev)
+    qx = torch.zeros(nx - 1, ny - 2, dtype=f64, device=dev)
+    qy = torch.zeros(nx - 2, ny - 1, dtype=f64, device=dev)
+    Cp = cfg.Cp0 * torch.ones(nx, ny, dtype=f64, device=dev)
+    T0 = initial_condition_2d(s)
+    if fused_push:
+        T = fabric_zeros((nx, ny))
+        T.copy_(T0)
+    else:
+        T = T0
+    n0 = native.launch_count()
+
+    plan = None
+    if fused_push:
+        fab = get_fabric()
+        plan = PushPlan(T)
+        bar_bank = fab.new_bank()
+        bar_epoch = 0
+        plan.begin()
+        lib = fab.lib
+    log0("Starting the time loop ...", end="")
+    for _ in range(int(cfg.nt)):
+        if on_gpu:
+            if fused_push:
+                # neighbours' Update! of the previous step has landed in my halo cells
+                sync = fab.sync_struct(plan.bank, plan.epoch)
+                native._check(lib.igg_wait_epoch(C.byref(sync), native._stream()))
+            native.flux2d(qx, qy, T, cfg.lam, _dx, _dy)
+            native.residual2d(dTdt, qx, qy, Cp, _dx, _dy)
+            if fused_push:
+                # every neighbour has finished reading its halo cells (its Flux!) before I overwrite them
+                bar_epoch += 1
+                bsync = fab.sync_struct(bar_bank, bar_epoch)
+                native._check(lib.igg_neighbor_barrier(C.byref(bsync), native._stream()))
+                native.update2d(T, dTdt, s.dt, push=plan.next(T))
+            else:
+                native.update2d(T, dTdt, s.dt)
+                if comm_needed:
+                    update_halo(T, transport=transport)
+        else:
+            ref.kp_step(T, Cp, qx, qy, dTdt, cfg.lam, s.dt, _dx, _dy)
+            if comm_needed:
+                update_halo(T)
+    if plan is not None:
+        plan.finish()
+    log0("done")
+    res = RunResult("kp", s.me, s.nprocs, s.dims, int(cfg.nt), T_local=T, launches=native.launch_count() - n0)
+    if cfg.do_vis:
+        visualise_2d(s, T, "kp", res)
+    if finalize:
+        finalize_global_grid()
+    return res
+
+
+def main(argv=None) -> None:
+    p = argparse.ArgumentParser(description=__doc__.split("\n")[0])
+    add_config_args(p)
+    diffusion2D_kp(config_from_args(p.parse_args(argv)))
+
+
+if __name__ == "__main__":
+    main()

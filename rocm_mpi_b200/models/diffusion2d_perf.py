@@ -1,0 +1,86 @@
+"""2-D heat diffusion, performance variant (``perf``): one fused double-buffered kernel per step.
+
+Behavioural counterpart of reference ``scripts/diffusion_2D_perf.jl``: fused ``diffusion_step!`` (``:3-13``),
+pointer swap (``:50``), ``update_halo!(T)`` (``:51``), ``tic()`` after the warm-up iterations (``:48``), ``toc()``
+and the ``T_eff`` report (``:53-58``), optional gather + heat map (``:59-63``).
+
+``--fused true`` (default): the halo exchange happens inside the stencil kernel (peer stores + epoch
+flags), so a step is ONE launch.  ``--fused false``: the reference's serial structure -- kernel, swap,
+``update_halo(T)`` over ``--transport`` (``nccl`` is the same-box baseline of BASELINE.md).
+
+Run:  ``torchrun --nproc-per-node 8 -m rocm_mpi_b200.models.diffusion2d_perf --nx 16384 --ny 16384 --nt 110``
+"""
+from __future__ import annotations
+
+import argparse
+import gc
+
+import torch
+
+from ..ops import native
+from ..parallel import a_eff, finalize_global_grid, global_grid, tic, toc
+from ..utils.config import DiffusionConfig, add_config_args, config_from_args
+from ..utils.profiling import nvtx_range
+from .common import RunResult, log0, setup_2d, visualise_2d
+from .solver import Diffusion2D
+
+__all__ = ["diffusion2D_perf", "run_timed", "main"]
+
+
+def run_timed(s: Diffusion2D, nt: int, warmup: int) -> float:
+    """The reference's time loop: ``tic()`` once ``warmup`` iterations are done, ``toc()`` at the end."""
+    s.begin()
+    gc_was = gc.isenabled()
+    gc.disable()                       # reference scripts/diffusion_2D_perf_hide.jl:73 (GC.enable(false))
+    try:
+        with nvtx_range("warmup"):
+            s.step(warmup)
+        tic()
+        with nvtx_range("timed_loop"):
+            s.step(nt - warmup)
+        wtime = toc()
+    finally:
+        if gc_was:
+            gc.enable()
+    s.finish()
+    return wtime
+
+
+def diffusion2D_perf(cfg: DiffusionConfig = None, mode: str = None, variant_name: str = "perf",
+                     finalize: bool = True) -> RunResult:
+    cfg = cfg or DiffusionConfig(nx=16384, ny=16384, nt=110, do_vis=False)
+    su = setup_2d(cfg)
+    g = global_grid()
+    if g.device_type != "cuda":
+        raise RuntimeError("diffusion2D_perf needs a CUDA device (use diffusion2d_ap for the CPU path)")
+    if mode is None:
+        mode = "fused" if cfg.fused else "plain"
+    n0 = native.launch_count()
+    s = Diffusion2D(cfg.nx, cfg.ny, lx=cfg.lx, ly=cfg.ly, lam=cfg.lam, Cp0=cfg.Cp0, mode=mode, variant=cfg.kernel,
+                    b_width=cfg.b_width[:2], transport=cfg.transport)
+    nt, warm = int(cfg.nt), min(int(cfg.warmup), max(int(cfg.nt) - 1, 0))
+    log0("Starting the time loop ...", end="")
+    wtime = run_timed(s, nt, warm)
+    log0("done")
+    A = a_eff((cfg.nx, cfg.ny))                      # reference scripts/diffusion_2D_perf.jl:55
+    wtime_it = wtime / max(nt - warm, 1)             # :56
+    T_eff = A / wtime_it                             # :57
+    log0("Executed %d steps in = %1.3e sec (@ T_eff = %1.2f GB/s) " % (nt, wtime, float("%.3g" % T_eff)))
+    res = RunResult(variant_name, su.me, su.nprocs, su.dims, nt, wtime=wtime, t_eff=T_eff, T_local=s.T,
+                    launches=native.launch_count() - n0)
+    if cfg.do_vis:
+        visualise_2d(su, s.T, variant_name, res)
+        log0("maximum(T_v) = %r" % res.max_T)        # reference scripts/diffusion_2D_perf_hide.jl:115
+    if finalize:
+        finalize_global_grid()
+    return res
+
+
+def main(argv=None) -> None:
+    p = argparse.ArgumentParser(description=__doc__.split("\n")[0])
+    add_config_args(p, DiffusionConfig(nx=16384, ny=16384, nt=110, do_vis=False))
+    diffusion2D_perf(config_from_args(p.parse_args(argv)))
+
+
+if __name__ == "__main__":
+    main()

@@ -6,3 +6,4 @@ from .halo import update_halo, halo_planes  # noqa: F401
 from .gather import gather, gather_interior, inner  # noqa: F401
 from .timing import tic, toc, t_eff, a_eff  # noqa: F401
 from .virtual import VirtualGrid  # noqa: F401
+from .hide import hide_communication, frame_regions, interior_region  # noqa: F401

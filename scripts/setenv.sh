@@ -1,0 +1,17 @@
+#!/bin/bash
+# Environment for a run (the counterpart of the reference's scripts/setenv.sh, which loads ROCm / MPI
+# modules and picks ROCm-aware vs standard MPI with IGG_ROCMAWARE_MPI, :11-18).
+REPO="$(cd "$(dirname "${BASH_SOURCE[0]}")/.." && pwd)"
+export PYTHONPATH="$REPO:${PYTHONPATH:-}"
+export MASTER_ADDR=${MASTER_ADDR:-127.0.0.1}
+export OMP_NUM_THREADS=${OMP_NUM_THREADS:-1}
+
+# Halo transport: peer (NVLink peer stores + flags; default), nccl (pack / NCCL p2p / unpack baseline),
+# host (pinned staging + gloo: the IGG_ROCMAWARE_MPI=0 analogue).
+export IGG_B200_TRANSPORT=${IGG_B200_TRANSPORT:-peer}
+
+# Kernel tuning knobs (defaults are the measured best on B200; see profiles/):
+#   IGG_TMA_CFG    4  = 256-thread CTAs, 8 rows per thread, Cp staged by TMA
+#   IGG_TILE_BAND  16 = tiles walked in bands of 16 tile columns (L2 reuse of halo rows/columns)
+#   IGG_L2_PROMO   2  = 128-byte L2 promotion for TMA loads
+echo "ENV setup done (transport: $IGG_B200_TRANSPORT)"

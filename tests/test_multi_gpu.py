@@ -22,3 +22,11 @@ def test_peer_fabric_and_solver_multi_gpu(nprocs, args):
         pytest.skip(f"needs {nprocs} GPUs")
     outs = run_workers("multi_gpu.py", nprocs, args, timeout=600)
     assert all("ok" in o for o in outs)
+
+
+@pytest.mark.parametrize("nprocs", [2, 4, 8])
+def test_apps_multi_gpu(nprocs, tmp_path):
+    if _ngpu() < nprocs:
+        pytest.skip(f"needs {nprocs} GPUs")
+    outs = run_workers("apps_multi_gpu.py", nprocs, (str(tmp_path), nprocs), timeout=900)
+    assert all("ok" in o for o in outs)

@@ -72,3 +72,33 @@ def test_oracle_3d_runs():
     T, dt = ref.oracle_3d(20, 18, 16, 5)
     assert T.shape == (20, 18, 16)
     assert 0 < float(T.max()) < 1
+
+
+def test_frame_regions_tile_the_frame_exactly():
+    from rocm_mpi_b200.parallel.hide import frame_regions, interior_region
+    for shape, bw in (((40, 36), (5, 3)), ((12, 50), (8, 2)), ((20, 18, 16), (3, 2, 4))):
+        cover = torch.zeros(shape, dtype=torch.int32)
+        for r in frame_regions(shape, bw):
+            cover[r] += 1
+        m = ref.frame_mask(shape, bw)
+        assert torch.equal(cover == 1, m) and int(cover.max()) <= 1
+        inner = interior_region(shape, bw)
+        if inner is not None:
+            assert int(cover[inner].sum()) == 0
+
+
+def test_hide_communication_cpu_single_rank_equals_full_step():
+    import rocm_mpi_b200 as igg
+    igg.init_global_grid(40, 36, 1, device_type="cpu", quiet=True)
+    torch.manual_seed(4)
+    T = torch.rand(40, 36, dtype=torch.float64)
+    Cp = torch.rand(40, 36, dtype=torch.float64) + 0.5
+    want = T.clone()
+    ref.perf_step(want, T, Cp, 1.0, 1e-3, 2.0, 3.0)
+    T2 = T.clone()
+
+    def step(region):
+        T2[region] = ref._perf_update(T, Cp, 1.0, 1e-3, 2.0, 3.0, region[0], region[1])
+
+    igg.hide_communication((5, 3), step, T2)
+    assert torch.equal(T2, want)
