@@ -175,6 +175,21 @@ __device__ __forceinline__ bool wait_flag_ge(const uint64_t* p, uint64_t want, u
     return true;
 }
 
+// Variant of wait_flag_ge that polls with relaxed system-scope loads and issues a single acquire fence
+// once the value is there (mode 1), or no fence at all (mode 2, timing experiments only).
+__device__ __forceinline__ bool wait_flag_ge_relaxed(const uint64_t* p, uint64_t want, uint64_t* err_word, int mode) {
+    uint64_t spins = 0;
+    while (ld_relaxed_sys(p) < want) {
+        __nanosleep(64);
+        if (++spins > (1ull << 26)) {
+            if (err_word) atomicExch((unsigned long long*)err_word, (unsigned long long)want | (1ull << 63));
+            return false;
+        }
+    }
+    if (mode == 1) asm volatile("fence.acq_rel.sys;" ::: "memory");
+    return true;
+}
+
 // streaming (evict-first) 16-byte / 8-byte global stores and read-only loads
 __device__ __forceinline__ void st_cs_f64x2(double* p, double a, double b) {
     asm volatile("st.global.cs.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");

@@ -59,13 +59,16 @@ __device__ __forceinline__ void signal_edges_2d(const igg_push2d& ps, const int*
 }
 
 // Before a tile reads halo planes: acquire the previous epoch from the face neighbours it touches.
-__device__ __forceinline__ void wait_faces_2d(const igg_push2d& ps, bool lo_x, bool hi_x, bool lo_y,
+// Returns true if any flag was actually acquired.
+__device__ __forceinline__ bool wait_faces_2d(const igg_push2d& ps, bool lo_x, bool hi_x, bool lo_y,
                                               bool hi_y) {
     const uint64_t want = ps.epoch - 1;
-    if (lo_x && ps.my_flag[0 * 3 + 1]) wait_flag_ge(ps.my_flag[0 * 3 + 1], want, ps.err_word);
-    if (hi_x && ps.my_flag[2 * 3 + 1]) wait_flag_ge(ps.my_flag[2 * 3 + 1], want, ps.err_word);
-    if (lo_y && ps.my_flag[1 * 3 + 0]) wait_flag_ge(ps.my_flag[1 * 3 + 0], want, ps.err_word);
-    if (hi_y && ps.my_flag[1 * 3 + 2]) wait_flag_ge(ps.my_flag[1 * 3 + 2], want, ps.err_word);
+    bool any = false;
+    if (lo_x && ps.my_flag[0 * 3 + 1]) { wait_flag_ge(ps.my_flag[0 * 3 + 1], want, ps.err_word); any = true; }
+    if (hi_x && ps.my_flag[2 * 3 + 1]) { wait_flag_ge(ps.my_flag[2 * 3 + 1], want, ps.err_word); any = true; }
+    if (lo_y && ps.my_flag[1 * 3 + 0]) { wait_flag_ge(ps.my_flag[1 * 3 + 0], want, ps.err_word); any = true; }
+    if (hi_y && ps.my_flag[1 * 3 + 2]) { wait_flag_ge(ps.my_flag[1 * 3 + 2], want, ps.err_word); any = true; }
+    return any;
 }
 
 // ---- 3-D -------------------------------------------------------------------------------------------
@@ -114,14 +117,16 @@ __device__ __forceinline__ void signal_edges_3d(const igg_push3d& ps, const int*
     }
 }
 
-__device__ __forceinline__ void wait_faces_3d(const igg_push3d& ps, const bool lo[3], const bool hi[3]) {
+__device__ __forceinline__ bool wait_faces_3d(const igg_push3d& ps, const bool lo[3], const bool hi[3]) {
     const uint64_t want = ps.epoch - 1;
     const int face_lo[3] = {(0 * 3 + 1) * 3 + 1, (1 * 3 + 0) * 3 + 1, (1 * 3 + 1) * 3 + 0};
     const int face_hi[3] = {(2 * 3 + 1) * 3 + 1, (1 * 3 + 2) * 3 + 1, (1 * 3 + 1) * 3 + 2};
+    bool any = false;
     for (int d = 0; d < 3; ++d) {
-        if (lo[d] && ps.my_flag[face_lo[d]]) wait_flag_ge(ps.my_flag[face_lo[d]], want, ps.err_word);
-        if (hi[d] && ps.my_flag[face_hi[d]]) wait_flag_ge(ps.my_flag[face_hi[d]], want, ps.err_word);
+        if (lo[d] && ps.my_flag[face_lo[d]]) { wait_flag_ge(ps.my_flag[face_lo[d]], want, ps.err_word); any = true; }
+        if (hi[d] && ps.my_flag[face_hi[d]]) { wait_flag_ge(ps.my_flag[face_hi[d]], want, ps.err_word); any = true; }
     }
+    return any;
 }
 
 }  // namespace igg

@@ -6,14 +6,18 @@
 // given -- the halo exchange that the reference performs afterwards with update_halo!
 // (scripts/diffusion_2D_perf.jl:51).  The design is new:
 //
-//  * variant 1 (product): a persistent kernel, one CTA per SM.  Each CTA walks a static list of
-//    32x128-cell tiles; thread 0 keeps a 3-stage ring of TMA loads in flight (the T tile with its
-//    one-cell halo -- out-of-bounds zero fill handles array edges -- and the matching Cp tile), all
-//    threads consume a stage after its mbarrier flips, computing from shared memory with a 3-row
-//    register window and 16-byte loads, and write T2 with 16-byte streaming stores.
+//  * variant 1 (product): a persistent, warp-specialised kernel, one CTA per SM.  A producer warp
+//    walks the CTA's static list of 32x128-cell tiles and keeps a 3-stage ring of TMA loads in
+//    flight (the T tile with its one-cell halo -- out-of-bounds zero fill handles array edges -- and
+//    the matching Cp tile); "full" mbarriers carry the TMA completion to the consumers and "empty"
+//    mbarriers hand finished stages back.  Sixteen consumer warps compute from shared memory with a
+//    3-row register window and 16-byte loads and write T2 with 16-byte streaming stores.  There is no
+//    CTA-wide barrier in the steady state.
 //  * boundary-frame tiles come first in the list, so edge cells are pushed into the neighbours'
 //    halo cells (peer stores over NVLink) and their epoch flag is released while the bulk of the
-//    interior is still being computed: communication is hidden inside ONE launch.
+//    interior is still being computed: communication is hidden inside ONE launch.  Waiting for the
+//    neighbours' previous epoch is done by the producer, ahead of the consumers.
+//  * optional in-kernel diagnostic {max, sum} of the written cells (no extra pass over the field).
 //  * variant 0: straightforward direct-load kernel with the same tiling, masks and push logic;
 //    it is the "recompiled baseline" flavour and the fallback for odd ny.
 //
@@ -36,9 +40,9 @@ constexpr int TP = BY + 4;      // smem pitch of the T tile (doubles)
 constexpr int T_TILE_BYTES = (BX + 2) * TP * 8;                      // 35904
 constexpr int T_TILE_PAD = (T_TILE_BYTES + 127) / 128 * 128;         // 35968
 constexpr int CP_TILE_BYTES = BX * BY * 8;                           // 32768
-// a pipeline stage holds the T tile and, when Cp is staged by TMA too, the Cp tile
-constexpr int stage_bytes(bool cp_tma) { return T_TILE_PAD + (cp_tma ? CP_TILE_BYTES : 0); }
-constexpr int smem_bytes(int stages, bool cp_tma) { return stages * stage_bytes(cp_tma) + 64; }   // + mbarriers
+constexpr int STAGE_BYTES = T_TILE_PAD + CP_TILE_BYTES;              // 68736
+constexpr int STAGES = 3;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 128;               // + mbarriers + tile ring
 
 // same layout as the scratch of igg_reduce_max_sum (csrc/misc.cu)
 struct DiagScratch {
@@ -65,13 +69,13 @@ struct Params {
     double lam, dt, _dx, _dy;
     const double* dev_params;   // optional {lam, dt, _dx, _dy} in device memory
     double* diag_out;           // optional {max, sum} of the written cells
-    struct DiagScratch* diag;   // block partials + ticket for diag_out
+    DiagScratch* diag;          // block partials + ticket for diag_out
     int mode, bwx, bwy;
     int i_hi, j_hi;             // tile row/column that contains x==nx-2 / y==ny-2
     TileSet ts;
     int has_push;
-    int l2_hints;               // 0 none, 1 Cp evict-first, 2 Cp evict-first + T evict-last
     int edge_tiles[9];
+    int side_nb[4];             // does ANY neighbour exist on the x-low / x-high / y-low / y-high side
     igg_push2d push;
 };
 
@@ -85,9 +89,7 @@ __device__ __forceinline__ void tile_of(const TileSet& ts, int t, int& i, int& j
             const int r = t - s.start;
             if (r >= 0 && r < s.w * s.h) {
                 if (s.band > 0) {
-                    // banded order: consecutive tile ids sweep `band` columns, then drop one tile row, so
-                    // the CTAs resident at one time hold vertical AND horizontal neighbours (halo rows
-                    // and columns are fetched from DRAM once and shared through L2)
+                    // banded order: consecutive tile ids sweep `band` columns, then drop one tile row
                     const int per_band = s.band * s.h;
                     const int b = r / per_band, rr = r - b * per_band;
                     const int jw = min(s.band, s.w - b * s.band);
@@ -112,87 +114,83 @@ __device__ __forceinline__ double update_cell(double c, double xm, double xp, do
     return c + dt * (cp * (-(qxr - qxl) * _dx - (qyt - qyb) * _dy));
 }
 
-// is (x,y) computed in this mode?  (interior test done by the caller)
+// is (x,y) in the boundary frame?  (interior test done by the caller)
 __device__ __forceinline__ bool in_frame(const Params& p, int x, int y) {
     return x <= p.bwx || x >= p.nx - 1 - p.bwx || y <= p.bwy || y >= p.ny - 1 - p.bwy;
 }
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// barrier among the consumer threads only (the producer warp never joins it)
+__device__ __forceinline__ void consumer_sync(int nthreads) {
+    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
+}
+
 // ------------------------------------------------------------------------------------------------
-// variant 1: persistent, TMA + mbarrier pipeline
+// variant 1: persistent, warp-specialised, TMA + mbarrier pipeline
 // ------------------------------------------------------------------------------------------------
-// RPT rows per thread; STAGES ring depth; CP_TMA: Cp tile staged by TMA (else read straight from global
-// into registers before the stage wait); MINB resident CTAs per SM the register budget is sized for.
-template <int RPT, int STAGES, bool CP_TMA, int MINB>
-__global__ void __launch_bounds__((BY / 2) * (BX / RPT), MINB)
+template <int RPT>   // rows per consumer thread
+__global__ void __launch_bounds__((BY / 2) * (BX / RPT) + 32, 1)
 diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapCp,
                   const __grid_constant__ Params p) {
+    constexpr int CONSUMERS = (BY / 2) * (BX / RPT);
+    constexpr int NCW = CONSUMERS / 32;
     extern __shared__ __align__(128) unsigned char smem[];
-    constexpr int STAGE_BYTES = stage_bytes(CP_TMA);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);   // TMA landed
+    uint64_t* empty = full + STAGES;                                              // consumers done
+    int2* tinfo = reinterpret_cast<int2*>(empty + STAGES);                        // (i, j) of the staged tile
     const int tid = threadIdx.x;
-    const int ntiles = p.ts.ntiles;
     const int first = blockIdx.x;
-    const int n_my = first < ntiles ? (ntiles - first + gridDim.x - 1) / gridDim.x : 0;
+    const int n_my = first < p.ts.ntiles ? (p.ts.ntiles - first + gridDim.x - 1) / gridDim.x : 0;
 
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], NCW);
+        }
         fence_mbar_init();
-        tma_prefetch_desc(&mapT);
-        tma_prefetch_desc(&mapCp);
     }
     __syncthreads();
 
-    auto issue = [&](int k) {
-        int i, j;
-        tile_of(p.ts, first + k * gridDim.x, i, j);
-        if (p.has_push) {
-            wait_faces_2d(p.push, i == 0, i == p.i_hi, j == 0, j == p.j_hi);
-            fence_proxy_async();
+    if (tid >= CONSUMERS) {
+        // ===== producer warp: one lane walks the tile list, waits for halos, issues TMA ===========
+        if (tid == CONSUMERS) {
+            tma_prefetch_desc(&mapT);
+            tma_prefetch_desc(&mapCp);
+            for (int k = 0; k < n_my; ++k) {
+                const int s = k % STAGES;
+                if (k >= STAGES) mbar_wait(&empty[s], ((k / STAGES) - 1) & 1);   // stage handed back
+                int i, j;
+                tile_of(p.ts, first + k * gridDim.x, i, j);
+                tinfo[s] = make_int2(i, j);
+                // only tiles that read a neighbour's halo plane wait; the proxy fence orders the acquired
+                // flag (generic proxy) before the TMA read (async proxy)
+                if (p.has_push && wait_faces_2d(p.push, i == 0, i == p.i_hi, j == 0, j == p.j_hi))
+                    fence_proxy_async();
+                unsigned char* st = smem + s * STAGE_BYTES;
+                mbar_arrive_expect_tx(&full[s], T_TILE_BYTES + CP_TILE_BYTES);   // also publishes tinfo[s]
+                tma_load_2d(st, &mapT, &full[s], j * BY - 2, i * BX - 1);
+                tma_load_2d(st + T_TILE_PAD, &mapCp, &full[s], j * BY, i * BX);
+            }
         }
-        const int s = k % STAGES;
-        unsigned char* st = smem + s * STAGE_BYTES;
-        mbar_arrive_expect_tx(&full[s], T_TILE_BYTES + (CP_TMA ? CP_TILE_BYTES : 0));
-        if (p.l2_hints) {
-            tma_load_2d_hint(st, &mapT, &full[s], j * BY - 2, i * BX - 1,
-                             p.l2_hints == 2 ? L2_EVICT_LAST : L2_EVICT_NORMAL);
-            if (CP_TMA) tma_load_2d_hint(st + T_TILE_PAD, &mapCp, &full[s], j * BY, i * BX, L2_EVICT_FIRST);
-        } else {
-            tma_load_2d(st, &mapT, &full[s], j * BY - 2, i * BX - 1);
-            if (CP_TMA) tma_load_2d(st + T_TILE_PAD, &mapCp, &full[s], j * BY, i * BX);
-        }
-    };
-
-    if (tid == 0) {
-        for (int k = 0; k < STAGES - 1 && k < n_my; ++k) issue(k);
+        return;
     }
 
+    // ===== consumer warps ============================================================================
     const int cp = tid % (BY / 2);   // column pair
     const int rg = tid / (BY / 2);   // row group
     const double lam = p.dev_params ? p.dev_params[0] : p.lam, dt = p.dev_params ? p.dev_params[1] : p.dt;
     const double _dx = p.dev_params ? p.dev_params[2] : p._dx, _dy = p.dev_params ? p.dev_params[3] : p._dy;
-
     const bool diag = p.diag_out != nullptr;
     double dmax = -INFINITY, dsum = 0.0;
 
     for (int k = 0; k < n_my; ++k) {
-        if (tid == 0 && k + STAGES - 1 < n_my) issue(k + STAGES - 1);
-        int i, j;
-        tile_of(p.ts, first + k * gridDim.x, i, j);
         const int s = k % STAGES;
-        // Cp without TMA: issue this thread's RPT 16-byte loads now, so their latency overlaps the wait
-        double2 cpr[RPT];
-        if (!CP_TMA) {
-            const int yq = j * BY + 2 * cp;
-#pragma unroll
-            for (int r = 0; r < RPT; ++r) {
-                int xq = i * BX + rg * RPT + r;
-                xq = xq < p.nx ? xq : p.nx - 1;                       // clamp: masked cells are never stored
-                const int yc = yq + 1 < p.ny ? yq : p.ny - 2;         // ny is even, so yq is even and this stays aligned
-                cpr[r] = __ldg(reinterpret_cast<const double2*>(p.Cp + (size_t)xq * p.ny + yc));
-            }
-        }
         mbar_wait(&full[s], (k / STAGES) & 1);
+        const int2 ij = tinfo[s];
+        const int i = ij.x, j = ij.y;
 
         // this thread's two cells sit at smem columns 2cp+2, 2cp+3 (16-byte aligned pair)
         const double* sT = reinterpret_cast<const double*>(smem + s * STAGE_BYTES) + (rg * RPT) * TP + 2 * cp + 2;
@@ -200,7 +198,10 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
                            (rg * RPT) * BY + 2 * cp;
         const int y = j * BY + 2 * cp;
         const int xb = i * BX + rg * RPT;
-        const bool edge_tile = p.has_push && (i == 0 || i == p.i_hi || j == 0 || j == p.j_hi);
+        // tile touches a side of the local domain behind which a neighbour exists
+        const bool e_xl = i == 0 && p.side_nb[0], e_xh = i == p.i_hi && p.side_nb[1];
+        const bool e_yl = j == 0 && p.side_nb[2], e_yh = j == p.j_hi && p.side_nb[3];
+        const bool edge_tile = p.has_push && (e_xl || e_xh || e_yl || e_yh);
         // column validity is fixed per thread
         const bool vy0 = (y >= 1) && (y <= p.ny - 2);
         const bool vy1 = (y + 1 <= p.ny - 2);
@@ -213,7 +214,7 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
             const double2 c = *reinterpret_cast<const double2*>(sT + (r + 2) * TP);
             const double bl = sT[(r + 1) * TP - 1];
             const double br = sT[(r + 1) * TP + 2];
-            const double2 cc = CP_TMA ? *reinterpret_cast<const double2*>(sC + r * BY) : cpr[r];
+            const double2 cc = *reinterpret_cast<const double2*>(sC + r * BY);
             const int x = xb + r;
             const double vA = update_cell(b.x, a.x, c.x, bl, b.y, cc.x, lam, dt, _dx, _dy);
             const double vB = update_cell(b.y, a.y, c.y, b.x, br, cc.y, lam, dt, _dx, _dy);
@@ -242,15 +243,18 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
             a = b;
             b = c;
         }
-        __syncthreads();   // stage s may be refilled; all remote stores of this tile were issued
-        if (edge_tile && tid == 0)
-            signal_edges_2d(p.push, p.edge_tiles, i == 0, i == p.i_hi, j == 0, j == p.j_hi);
+        // hand the stage back to the producer: one arrival per consumer warp
+        __syncwarp();
+        if ((tid & 31) == 0) mbar_arrive(&empty[s]);
+        if (edge_tile) {
+            consumer_sync(CONSUMERS);   // every remote store of this tile has been issued
+            if (tid == 0) signal_edges_2d(p.push, p.edge_tiles, e_xl, e_xh, e_yl, e_yh);
+        }
     }
 
     // fused diagnostic: CTA partial -> scratch, last CTA (ticket) folds all partials in a fixed order
     if (diag) {
-        constexpr int NW = (BY / 2) * (BX / RPT) / 32;
-        double* red = reinterpret_cast<double*>(smem);          // all stages have been consumed
+        __shared__ double red[64];
         __shared__ bool is_last;
         auto block_fold = [&](double& mx, double& sm) {
 #pragma unroll
@@ -259,17 +263,17 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
                 sm += __shfl_xor_sync(0xffffffffu, sm, off);
             }
             if ((tid & 31) == 0) { red[tid >> 5] = mx; red[32 + (tid >> 5)] = sm; }
-            __syncthreads();
+            consumer_sync(CONSUMERS);
             if (tid < 32) {
-                mx = tid < NW ? red[tid] : -INFINITY;
-                sm = tid < NW ? red[32 + tid] : 0.0;
+                mx = tid < NCW ? red[tid] : -INFINITY;
+                sm = tid < NCW ? red[32 + tid] : 0.0;
 #pragma unroll
                 for (int off = 16; off > 0; off >>= 1) {
                     mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
                     sm += __shfl_xor_sync(0xffffffffu, sm, off);
                 }
             }
-            __syncthreads();
+            consumer_sync(CONSUMERS);
         };
         block_fold(dmax, dsum);
         if (tid == 0) {
@@ -278,12 +282,12 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
             __threadfence();
             is_last = atomicAdd(&p.diag->ticket, 1u) == gridDim.x - 1;
         }
-        __syncthreads();
+        consumer_sync(CONSUMERS);
         if (is_last) {
             __threadfence();
             dmax = -INFINITY;
             dsum = 0.0;
-            for (unsigned int b2 = tid; b2 < gridDim.x; b2 += blockDim.x) {
+            for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS) {
                 dmax = fmax(dmax, p.diag->pmax[b2]);
                 dsum += p.diag->psum[b2];
             }
@@ -304,13 +308,15 @@ constexpr int DBX = 16;
 __global__ void __launch_bounds__(256) diff2d_direct_kernel(const __grid_constant__ Params p) {
     int i, j;
     tile_of(p.ts, blockIdx.x, i, j);
-    // here tiles are BX x BY as well; 256 threads = 2 row groups x 128 columns, 16 rows each
+    // tiles are BX x BY as well; 256 threads = 2 row groups x 128 columns, 16 rows each
     const int tid = threadIdx.x;
     const int y = j * BY + (tid % BY);
     const int xb = i * BX + (tid / BY) * DBX;
-    const bool edge_tile = p.has_push && (i == 0 || i == p.i_hi || j == 0 || j == p.j_hi);
-    if (p.has_push) {
-        if (tid == 0) wait_faces_2d(p.push, i == 0, i == p.i_hi, j == 0, j == p.j_hi);
+    const bool e_xl = i == 0 && p.side_nb[0], e_xh = i == p.i_hi && p.side_nb[1];
+    const bool e_yl = j == 0 && p.side_nb[2], e_yh = j == p.j_hi && p.side_nb[3];
+    const bool edge_tile = p.has_push && (e_xl || e_xh || e_yl || e_yh);
+    if (edge_tile) {
+        if (tid == 0) wait_faces_2d(p.push, e_xl, e_xh, e_yl, e_yh);
         __syncthreads();
     }
     const bool vy = (y >= 1) && (y <= p.ny - 2);
@@ -344,7 +350,7 @@ __global__ void __launch_bounds__(256) diff2d_direct_kernel(const __grid_constan
     }
     if (edge_tile) {
         __syncthreads();
-        if (tid == 0) signal_edges_2d(p.push, p.edge_tiles, i == 0, i == p.i_hi, j == 0, j == p.j_hi);
+        if (tid == 0) signal_edges_2d(p.push, p.edge_tiles, e_xl, e_xh, e_yl, e_yh);
     }
 }
 
@@ -363,29 +369,21 @@ static void add_seg(TileSet& ts, int i0, int i1, int j0, int j1, int band = 0) {
     ts.ntiles += s.w * s.h;
 }
 
-static int tma_config() {
-    static int v = -1;
-    if (v < 0) {
-        const char* e = getenv("IGG_TMA_CFG");
-        v = e ? atoi(e) : 4;
-    }
-    return v;
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
 }
 
-static int l2_hints() {
+// tuning knobs (see scripts/setenv.sh); read once
+static int tma_rows_per_thread() {
     static int v = -1;
-    if (v < 0) {
-        const char* e = getenv("IGG_L2_HINTS");
-        v = e ? atoi(e) : 0;
-    }
+    if (v < 0) v = env_int("IGG_TMA_RPT", 4);
     return v;
 }
-
 static int tile_band() {
     static int v = -1;
     if (v < 0) {
-        const char* e = getenv("IGG_TILE_BAND");
-        v = e ? atoi(e) : 16;
+        v = env_int("IGG_TILE_BAND", 0);
         if (v < 0) v = 0;
     }
     return v;
@@ -422,6 +420,21 @@ static void build_tiles(TileSet& ts, int nx, int ny, int mode, int bwx, int bwy)
     if (mode == 0) add_seg(ts, a0 + 1, a1 - 1, b0 + 1, b1 - 1, band);
 }
 
+template <int RPT>
+static int launch_tma(const CUtensorMap& mT, const CUtensorMap& mC, const Params& p, cudaStream_t st) {
+    auto kern = diff2d_tma_kernel<RPT>;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    IGG_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    const int sms = igg::sm_count();
+    const int grid = p.ts.ntiles < sms ? p.ts.ntiles : sms;
+    kern<<<grid, (BY / 2) * (BX / RPT) + 32, SMEM_BYTES, st>>>(mT, mC, p);
+    return 0;
+}
 
 }  // namespace
 
@@ -450,14 +463,22 @@ extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* C
     build_tiles(p.ts, nx, ny, mode, bwx, bwy);
     if (p.ts.ntiles == 0) return 0;
     p.has_push = push ? 1 : 0;
-    p.l2_hints = l2_hints();
     const int nti = p.i_hi + 1, ntj = p.j_hi + 1;
     for (int sx = -1; sx <= 1; ++sx)
         for (int sy = -1; sy <= 1; ++sy)
             p.edge_tiles[(sx + 1) * 3 + (sy + 1)] = (sx != 0 && sy != 0) ? 1 : (sx != 0 ? ntj : nti);
+    for (int k = 0; k < 4; ++k) p.side_nb[k] = 0;
     if (push) {
         p.push = *push;
         IGG_REQUIRE(push->epoch >= 1, "igg_diffusion2d_step: push epoch must be >= 1");
+        for (int sx = -1; sx <= 1; ++sx)
+            for (int sy = -1; sy <= 1; ++sy) {
+                if (!push->peer_dst[(sx + 1) * 3 + (sy + 1)]) continue;
+                if (sx == -1) p.side_nb[0] = 1;
+                if (sx == 1) p.side_nb[1] = 1;
+                if (sy == -1) p.side_nb[2] = 1;
+                if (sy == 1) p.side_nb[3] = 1;
+            }
     } else {
         memset(&p.push, 0, sizeof(p.push));
     }
@@ -476,31 +497,12 @@ extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* C
         if (rc) return rc;
         rc = igg::get_tensor_map_f64(Cp, 2, dims, boxC, &mC);
         if (rc) return rc;
-        int dev = 0;
-        IGG_CUDA_OK(cudaGetDevice(&dev));
-        const int grid_cap = igg::sm_count();
-#define IGG_LAUNCH_TMA(RPT_, ST_, CPT_, MINB_)                                                                  \
-        do {                                                                                                        \
-            auto kern = diff2d_tma_kernel<RPT_, ST_, CPT_, MINB_>;                                                  \
-            constexpr int SM_ = smem_bytes(ST_, CPT_);                                                              \
-            static bool attr_set[64] = {false};                                                                     \
-            if (dev < 0 || dev >= 64 || !attr_set[dev]) {                                                           \
-                IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_));          \
-                if (dev >= 0 && dev < 64) attr_set[dev] = true;                                                     \
-            }                                                                                                       \
-            const int cap = grid_cap * MINB_;                                                                       \
-            const int grid = p.ts.ntiles < cap ? p.ts.ntiles : cap;                                                 \
-            kern<<<grid, (BY / 2) * (BX / RPT_), SM_, st>>>(mT, mC, p);                                             \
-        } while (0)
-        switch (tma_config()) {
-            case 1: IGG_LAUNCH_TMA(4, 3, false, 2); break;   // 512 thr, Cp direct, 2 CTA/SM
-            case 2: IGG_LAUNCH_TMA(8, 3, false, 2); break;   // 256 thr, Cp direct, 2 CTA/SM
-            case 3: IGG_LAUNCH_TMA(8, 2, false, 3); break;   // 256 thr, Cp direct, 3 CTA/SM
-            case 4: IGG_LAUNCH_TMA(8, 3, true, 1); break;    // 256 thr, Cp by TMA, 1 CTA/SM
-            case 5: IGG_LAUNCH_TMA(16, 3, true, 1); break;   // 128 thr, Cp by TMA, 1 CTA/SM
-            default: IGG_LAUNCH_TMA(4, 3, true, 1); break;   // 512 thr, Cp by TMA, 1 CTA/SM
+        switch (tma_rows_per_thread()) {
+            case 4: rc = launch_tma<4>(mT, mC, p, st); break;    // 16 consumer warps
+            case 16: rc = launch_tma<16>(mT, mC, p, st); break;  // 4 consumer warps
+            default: rc = launch_tma<8>(mT, mC, p, st); break;   // 8 consumer warps
         }
-#undef IGG_LAUNCH_TMA
+        if (rc) return rc;
         IGG_LAUNCH_CHECK();
     } else {
         diff2d_direct_kernel<<<p.ts.ntiles, 256, 0, st>>>(p);

@@ -46,6 +46,7 @@ struct Params3 {
     TileSet3 ts;
     int has_push;
     int edge_tiles[27];
+    int side_nb[3][2];        // does ANY neighbour exist on the low / high side of each dimension
     igg_push3d push;
 };
 
@@ -106,8 +107,9 @@ diff3d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
     __syncthreads();
 
     auto flags_of = [&](int i, int j, int k, bool lo[3], bool hi[3]) {
-        lo[0] = i == 0; lo[1] = j == 0; lo[2] = k == 0;
-        hi[0] = i == p.t_hi[0]; hi[1] = j == p.t_hi[1]; hi[2] = k == p.t_hi[2];
+        lo[0] = i == 0 && p.side_nb[0][0]; lo[1] = j == 0 && p.side_nb[1][0]; lo[2] = k == 0 && p.side_nb[2][0];
+        hi[0] = i == p.t_hi[0] && p.side_nb[0][1]; hi[1] = j == p.t_hi[1] && p.side_nb[1][1];
+        hi[2] = k == p.t_hi[2] && p.side_nb[2][1];
     };
     auto issue = [&](int q) {
         int i, j, k;
@@ -115,8 +117,7 @@ diff3d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
         if (p.has_push) {
             bool lo[3], hi[3];
             flags_of(i, j, k, lo, hi);
-            wait_faces_3d(p.push, lo, hi);
-            fence_proxy_async();
+            if (wait_faces_3d(p.push, lo, hi)) fence_proxy_async();
         }
         const int s = q % STAGES3_USED;
         unsigned char* st = smem + s * STAGE3_BYTES;
@@ -180,11 +181,12 @@ diff3d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
 __global__ void __launch_bounds__(256) diff3d_direct_kernel(const __grid_constant__ Params3 p) {
     int i, j, k;
     tile_of3(p.ts, blockIdx.x, i, j, k);
-    bool lo[3] = {i == 0, j == 0, k == 0};
-    bool hi[3] = {i == p.t_hi[0], j == p.t_hi[1], k == p.t_hi[2]};
+    bool lo[3] = {i == 0 && p.side_nb[0][0], j == 0 && p.side_nb[1][0], k == 0 && p.side_nb[2][0]};
+    bool hi[3] = {i == p.t_hi[0] && p.side_nb[0][1], j == p.t_hi[1] && p.side_nb[1][1],
+                  k == p.t_hi[2] && p.side_nb[2][1]};
     const bool edge_tile = p.has_push && (lo[0] || lo[1] || lo[2] || hi[0] || hi[1] || hi[2]);
     const int tid = threadIdx.x;
-    if (p.has_push) {
+    if (edge_tile) {
         if (tid == 0) wait_faces_3d(p.push, lo, hi);
         __syncthreads();
     }
@@ -303,9 +305,18 @@ extern "C" int igg_diffusion3d_step(const double* T, double* T2, const double* C
             for (int sz = -1; sz <= 1; ++sz)
                 p.edge_tiles[((sx + 1) * 3 + (sy + 1)) * 3 + (sz + 1)] =
                     (sx ? 1 : nt[0]) * (sy ? 1 : nt[1]) * (sz ? 1 : nt[2]);
+    memset(p.side_nb, 0, sizeof(p.side_nb));
     if (push) {
         p.push = *push;
         IGG_REQUIRE(push->epoch >= 1, "igg_diffusion3d_step: push epoch must be >= 1");
+        for (int o = 0; o < 27; ++o) {
+            if (!push->peer_dst[o]) continue;
+            const int s3[3] = {o / 9 - 1, (o / 3) % 3 - 1, o % 3 - 1};
+            for (int d = 0; d < 3; ++d) {
+                if (s3[d] == -1) p.side_nb[d][0] = 1;
+                if (s3[d] == 1) p.side_nb[d][1] = 1;
+            }
+        }
     } else {
         memset(&p.push, 0, sizeof(p.push));
     }

@@ -212,8 +212,38 @@ class TorchComm(Comm):
         return out
 
     def finalize(self) -> None:
+        """Release the communicator.
+
+        The process group itself is torn down once, at interpreter exit: an application may call
+        ``finalize_global_grid()`` and ``init_global_grid()`` again in the same process (several runs in one
+        script), and re-creating a process group on the same rendezvous port is neither cheap nor
+        reliable.  (MPI cannot be re-initialised at all; this is the more forgiving behaviour.)
+        """
         if self._owns_pg and self._dist.is_initialized():
-            self._dist.destroy_process_group()
+            _destroy_pg_at_exit()
+
+
+_atexit_registered = False
+
+
+def _destroy_pg_at_exit() -> None:
+    global _atexit_registered
+    if _atexit_registered:
+        return
+    _atexit_registered = True
+    import atexit
+
+    def _destroy():
+        import torch.distributed as dist
+        try:
+            if dist.is_available() and dist.is_initialized():
+                if torch.cuda.is_available():
+                    torch.cuda.synchronize()
+                dist.destroy_process_group()
+        except Exception:
+            pass
+
+    atexit.register(_destroy)
 
 
 def make_comm(device_type: str, init_dist: bool = True) -> Comm:

@@ -11,7 +11,7 @@ export OMP_NUM_THREADS=${OMP_NUM_THREADS:-1}
 export IGG_B200_TRANSPORT=${IGG_B200_TRANSPORT:-peer}
 
 # Kernel tuning knobs (defaults are the measured best on B200; see profiles/):
-#   IGG_TMA_CFG    4  = 256-thread CTAs, 8 rows per thread, Cp staged by TMA
-#   IGG_TILE_BAND  16 = tiles walked in bands of 16 tile columns (L2 reuse of halo rows/columns)
+#   IGG_TMA_RPT    4  = rows per consumer thread (16 consumer warps + 1 producer warp per CTA)
+#   IGG_TILE_BAND  0  = row-major tile order (N > 0: bands of N tile columns)
 #   IGG_L2_PROMO   2  = 128-byte L2 promotion for TMA loads
 echo "ENV setup done (transport: $IGG_B200_TRANSPORT)"

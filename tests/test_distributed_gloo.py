@@ -26,3 +26,8 @@ def test_ap_app_4_ranks_bit_exact(tmp_path):
 def test_ap_app_8_ranks_4x2_layout(tmp_path):
     outs = run_workers("ap_gloo.py", 8, (65, 128, 4, 2, 40, str(tmp_path)), timeout=600)
     assert all("ok" in o for o in outs)
+
+
+def test_grid_can_be_reinitialised_in_one_process():
+    outs = run_workers("reinit_gloo.py", 2)
+    assert all("ok" in o for o in outs)
