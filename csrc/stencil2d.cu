@@ -389,7 +389,8 @@ static int tile_band() {
     return v;
 }
 
-static void build_tiles(TileSet& ts, int nx, int ny, int mode, int bwx, int bwy) {
+static void build_tiles(TileSet& ts, int nx, int ny, int mode, int bwx, int bwy, const int BX = ::BX,
+                        const int BY = ::BY) {
     ts.nseg = 0;
     ts.ntiles = 0;
     const int band = tile_band();
@@ -508,5 +509,155 @@ extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* C
         diff2d_direct_kernel<<<p.ts.ntiles, 256, 0, st>>>(p);
         IGG_LAUNCH_CHECK();
     }
+    return 0;
+}
+
+// ================================================================================================
+// Persistent multi-step kernel for latency-bound (small) local grids -- beyond the reference.
+//
+// The reference pays, per time step, three kernel launches with a host wait after each
+// (scripts/diffusion_2D_kp.jl:88-90) or one launch + a blocking update_halo! (scripts/diffusion_2D_perf.jl:49-51);
+// at 128 x 128 cells per GPU that is pure launch / synchronisation latency.  Here ONE cooperative launch
+// runs `nsteps` steps: every CTA owns a fixed set of tiles, edge cells are pushed to the neighbours'
+// halo cells and the epoch released exactly as in the per-step kernels, and the steps are separated by
+// a grid barrier (a monotonic counter in global memory).  Fields stay L2-resident; reads of the field
+// use ld.global.cg because L1 is not coherent with what other SMs (or peers) wrote in the previous step.
+// ================================================================================================
+namespace {
+
+struct MSParams {
+    Params p;                   // step 0 reads p.T and writes p.T2; push.peer_dst = neighbours' T2
+    double* peer_dst_odd[9];    // odd steps write T: neighbours' T
+    int nsteps;
+    unsigned long long* gbar;   // grid-barrier counter (monotonic)
+    unsigned long long gbar_base;
+};
+
+constexpr int MBX = 8;          // tile rows of the multi-step kernel: small tiles = many CTAs on a small grid
+constexpr int MROWS = MBX / 2;  // rows per thread (256 threads = 2 row groups x 128 columns)
+
+__global__ void __launch_bounds__(256) diff2d_multistep_kernel(const __grid_constant__ MSParams q) {
+    const Params& p = q.p;
+    const int tid = threadIdx.x;
+    const int nx = p.nx, ny = p.ny;
+    for (int step = 0; step < q.nsteps; ++step) {
+        const bool even = (step & 1) == 0;
+        const double* __restrict__ src = even ? p.T : p.T2;
+        double* __restrict__ dst = even ? p.T2 : const_cast<double*>(p.T);
+        double* const* peers = even ? p.push.peer_dst : q.peer_dst_odd;
+        const uint64_t epoch = p.push.epoch + (uint64_t)step;
+        for (int t = blockIdx.x; t < p.ts.ntiles; t += gridDim.x) {
+            int i, j;
+            tile_of(p.ts, t, i, j);
+            const int y = j * BY + (tid % BY);
+            const int xb = i * MBX + (tid / BY) * MROWS;
+            const bool e_xl = i == 0 && p.side_nb[0], e_xh = i == p.i_hi && p.side_nb[1];
+            const bool e_yl = j == 0 && p.side_nb[2], e_yh = j == p.j_hi && p.side_nb[3];
+            const bool edge_tile = p.has_push && (e_xl || e_xh || e_yl || e_yh);
+            if (edge_tile) {
+                if (tid == 0) wait_faces_2d_epoch(p.push, e_xl, e_xh, e_yl, e_yh, epoch - 1);
+                __syncthreads();
+            }
+            if (y >= 1 && y <= ny - 2) {
+                // all loads of this thread are independent: one L2 round trip per step, not one per row
+                double col[MROWS + 2], lf[MROWS], rt[MROWS], cpv[MROWS];
+#pragma unroll
+                for (int r = 0; r < MROWS + 2; ++r) {
+                    int x = xb - 1 + r;
+                    x = x < 0 ? 0 : (x > nx - 1 ? nx - 1 : x);
+                    col[r] = __ldcg(src + (size_t)x * ny + y);
+                }
+#pragma unroll
+                for (int r = 0; r < MROWS; ++r) {
+                    int x = xb + r;
+                    x = x > nx - 1 ? nx - 1 : x;
+                    lf[r] = __ldcg(src + (size_t)x * ny + y - 1);
+                    rt[r] = __ldcg(src + (size_t)x * ny + y + 1);
+                    cpv[r] = p.Cp[(size_t)x * ny + y];
+                }
+#pragma unroll
+                for (int r = 0; r < MROWS; ++r) {
+                    const int x = xb + r;
+                    if (x >= 1 && x <= nx - 2) {
+                        const double v = update_cell(col[r + 1], col[r], col[r + 2], lf[r], rt[r], cpv[r], p.lam, p.dt,
+                                                     p._dx, p._dy);
+                        dst[(size_t)x * ny + y] = v;
+                        if (edge_tile) push_cell_2d_to(peers, nx, ny, x, y, v);
+                    }
+                }
+            }
+            if (edge_tile) {
+                __syncthreads();
+                if (tid == 0) signal_edges_2d_epoch(p.push, p.edge_tiles, e_xl, e_xh, e_yl, e_yh, epoch);
+            }
+        }
+        // grid barrier: everybody has finished reading `src` and writing `dst`
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            atomicAdd(q.gbar, 1ull);
+            const unsigned long long want = q.gbar_base + (unsigned long long)(step + 1) * gridDim.x;
+            while (*((volatile unsigned long long*)q.gbar) < want) {
+            }
+            __threadfence();
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+extern "C" int igg_diffusion2d_multistep(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
+                                         double _dx, double _dy, int nsteps, const igg_push2d* push_even,
+                                         double* const* peer_dst_odd, unsigned long long* grid_barrier,
+                                         unsigned long long grid_barrier_base, int* grid_size_out, void* stream) {
+    IGG_REQUIRE(T && T2 && Cp && grid_barrier, "igg_diffusion2d_multistep: null pointer");
+    IGG_REQUIRE(nx >= 3 && ny >= 3 && nsteps >= 1, "igg_diffusion2d_multistep: bad sizes");
+    IGG_REQUIRE(!push_even || peer_dst_odd, "igg_diffusion2d_multistep: a push needs both destination tables");
+    MSParams q;
+    Params& p = q.p;
+    memset(&q, 0, sizeof(q));
+    p.T = T; p.T2 = T2; p.Cp = Cp; p.nx = nx; p.ny = ny;
+    p.lam = lam; p.dt = dt; p._dx = _dx; p._dy = _dy;
+    p.mode = 0; p.bwx = 1; p.bwy = 1;
+    p.i_hi = (nx - 2) / MBX;
+    p.j_hi = (ny - 2) / BY;
+    build_tiles(p.ts, nx, ny, 0, 1, 1, MBX, BY);
+    p.has_push = push_even ? 1 : 0;
+    const int nti = p.i_hi + 1, ntj = p.j_hi + 1;
+    for (int sx = -1; sx <= 1; ++sx)
+        for (int sy = -1; sy <= 1; ++sy)
+            p.edge_tiles[(sx + 1) * 3 + (sy + 1)] = (sx != 0 && sy != 0) ? 1 : (sx != 0 ? ntj : nti);
+    if (push_even) {
+        p.push = *push_even;
+        IGG_REQUIRE(push_even->epoch >= 1, "igg_diffusion2d_multistep: push epoch must be >= 1");
+        for (int o = 0; o < 9; ++o) {
+            q.peer_dst_odd[o] = peer_dst_odd[o];
+            if (!push_even->peer_dst[o]) continue;
+            IGG_REQUIRE(peer_dst_odd[o] != nullptr, "igg_diffusion2d_multistep: destination tables disagree");
+            const int sx = o / 3 - 1, sy = o % 3 - 1;
+            if (sx == -1) p.side_nb[0] = 1;
+            if (sx == 1) p.side_nb[1] = 1;
+            if (sy == -1) p.side_nb[2] = 1;
+            if (sy == 1) p.side_nb[3] = 1;
+        }
+    }
+    q.nsteps = nsteps;
+    q.gbar = grid_barrier;
+    q.gbar_base = grid_barrier_base;
+    // all CTAs must be co-resident (they wait for one another): cooperative launch, grid <= what fits
+    int dev = 0, coop = 0, per_sm = 0;
+    IGG_CUDA_OK(cudaGetDevice(&dev));
+    IGG_CUDA_OK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    IGG_REQUIRE(coop, "igg_diffusion2d_multistep: device does not support cooperative launches");
+    IGG_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, diff2d_multistep_kernel, 256, 0));
+    int grid = igg::sm_count() * (per_sm > 0 ? 1 : 0);
+    IGG_REQUIRE(grid > 0, "igg_diffusion2d_multistep: kernel does not fit on an SM");
+    if (grid > p.ts.ntiles) grid = p.ts.ntiles;
+    if (grid_size_out) *grid_size_out = grid;
+    void* args[] = {(void*)&q};
+    IGG_CUDA_OK(cudaLaunchCooperativeKernel((const void*)diff2d_multistep_kernel, dim3(grid), dim3(256), args, 0,
+                                            (cudaStream_t)stream));
+    IGG_LAUNCH_CHECK();
     return 0;
 }

@@ -75,6 +75,18 @@ int igg_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, 
                          double dt, double _dx, double _dy, const igg_step_opts* opts, int mode, int bwx,
                          int bwy, int variant, const igg_push2d* push, void* stream);
 
+/* `nsteps` fused steps in ONE cooperative launch, for local grids so small that a step is pure launch
+ * latency (reference loop: scripts/diffusion_2D_kp.jl:87-92 at 128 x 128; no reference counterpart for the
+ * single-launch form).  Step s reads T (s even) or T2 (s odd) and writes the other; after the call the
+ * result is in T2 if nsteps is odd, else in T.  `push_even` (may be NULL) describes the pushes of even
+ * steps (destinations: the neighbours' T2) with `epoch` = epoch of the first step; `peer_dst_odd[9]` are
+ * the destinations of odd steps (the neighbours' T).  `grid_barrier`: device counter private to this rank,
+ * `grid_barrier_base` its current value; the launch adds nsteps * (*grid_size_out) to it. */
+int igg_diffusion2d_multistep(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
+                              double _dx, double _dy, int nsteps, const igg_push2d* push_even,
+                              double* const* peer_dst_odd, unsigned long long* grid_barrier,
+                              unsigned long long grid_barrier_base, int* grid_size_out, void* stream);
+
 /* ---- 2-D diffusion, three-kernel form (reference scripts/diffusion_2D_kp.jl:16-54) ------------ */
 int igg_flux2d(double* qx, double* qy, const double* T, int nx, int ny, double lam, double _dx,
                double _dy, void* stream);

@@ -10,6 +10,8 @@ offers three ways to advance, all producing the same field:
            (``scripts/diffusion_2D_perf_hide.jl:94-101``): boundary frame of width ``b_width`` on a
            high-priority stream (pushing edges as it goes), interior on a low-priority stream,
            join, swap.
+``persistent``  for small local grids: ``step(n)`` is ONE cooperative launch that runs all ``n`` steps with
+           in-kernel grid barriers and the same in-kernel halo pushes (no per-step launch latency).
 ``plain``  the reference's serial structure (``scripts/diffusion_2D_perf.jl:49-51``): full kernel,
            swap, ``update_halo(T)`` over the chosen transport (``nccl`` = the same-box baseline).
 
@@ -41,8 +43,8 @@ class Diffusion2D:
             raise RuntimeError("Diffusion2D runs on CUDA devices; use models.diffusion2d_ap on CPU")
         if (nx, ny) != tuple(g.nxyz[:2]):
             raise ValueError("nx, ny must be the local sizes given to init_global_grid")
-        if mode not in ("fused", "hide", "plain"):
-            raise ValueError("mode must be fused | hide | plain")
+        if mode not in ("fused", "hide", "plain", "persistent"):
+            raise ValueError("mode must be fused | hide | plain | persistent")
         native.require()
         self.g = g
         self.nx, self.ny = nx, ny
@@ -54,7 +56,9 @@ class Diffusion2D:
         self.b_width = (int(b_width[0]), int(b_width[1]))
         dev = g.device
         self.transport = transport or default_transport(torch.empty(0, device=dev))
-        self.uses_peer = mode in ("fused", "hide") or self.transport == "peer"
+        self.uses_peer = mode in ("fused", "hide", "persistent") or self.transport == "peer"
+        if mode == "persistent":
+            variant = self.variant = "direct"      # the multi-step kernel reads the field through L2 directly
         if variant == "tma" and ny % 2:
             raise ValueError("variant 'tma' needs an even ny (16-byte row pitch); use variant='direct'")
         # fields: peer-addressable when any peer path is in use
@@ -68,8 +72,10 @@ class Diffusion2D:
         self._init_condition(host_ic)
         self.T2.copy_(self.T)                      # reference scripts/diffusion_2D_perf.jl:36
         self.plan: Optional[PushPlan] = None
-        if mode in ("fused", "hide"):
+        if mode in ("fused", "hide", "persistent"):
             self.plan = PushPlan(self.T, self.T2)
+        self._gbar = torch.zeros(1, dtype=torch.int64, device=dev)
+        self._gbar_base = 0
         self._running = False
         self.steps_done = 0
         # streams for the hide structure (reference perf_hide.jl:63-68: HIGH / LOW priority queues)
@@ -136,6 +142,23 @@ class Diffusion2D:
             self.begin()
         if diag_out is not None and not self.fused_diag:
             raise ValueError("in-kernel diagnostics need mode='fused' or 'plain' with variant='tma'")
+        if self.mode == "persistent":
+            if dev_params is not None:
+                raise ValueError("mode='persistent' takes its parameters by value")
+            if n <= 0:
+                return
+            pe = po = None
+            if self.plan.fab.neighbors:
+                pe, po = self.plan._desc[self.T2.data_ptr()], self.plan._desc[self.T.data_ptr()]
+                pe.epoch = self.plan.epoch + 1
+            grid = native.diffusion2d_multistep(self.T, self.T2, self.Cp, self.lam, self.dt, self._dx, self._dy, n,
+                                                self._gbar, self._gbar_base, pe, po)
+            self._gbar_base += n * grid
+            self.plan.epoch += n if self.plan.fab.neighbors else 0
+            if n % 2:
+                self.T, self.T2 = self.T2, self.T
+            self.steps_done += n
+            return
         for _ in range(n):
             if self.mode == "fused":
                 self._kernel(0, self.plan.next(self.T2), dev_params, diag_out)
@@ -194,7 +217,7 @@ class Diffusion2D:
             return 1
         if self.mode == "hide":
             return 2
-        return 1
+        return 1      # "persistent": one launch per step() call, however many steps
 
     def max_sum(self) -> Tuple[float, float]:
         out = native.reduce_max_sum(self.T.view(-1))

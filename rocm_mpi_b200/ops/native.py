@@ -67,6 +67,8 @@ def _declare(lib) -> None:
         "igg_launch_count": ([], C.c_ulonglong),
         "igg_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d, C.POINTER(StepOpts), i, i, i, i,
                                  C.POINTER(Push2D), vp], i),
+        "igg_diffusion2d_multistep": ([vp, vp, vp, i, i, d, d, d, d, i, C.POINTER(Push2D), C.POINTER(vp), vp,
+                                      C.c_ulonglong, C.POINTER(i), vp], i),
         "igg_flux2d": ([vp, vp, vp, i, i, d, d, d, vp], i),
         "igg_residual2d": ([vp, vp, vp, vp, i, i, d, d, vp], i),
         "igg_update2d": ([vp, vp, i, i, d, C.POINTER(Push2D), vp], i),
@@ -192,6 +194,25 @@ def diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: f
                                     C.byref(opts) if opts is not None else None,
                                     mode, int(b_width[0]), int(b_width[1]), VARIANTS[variant],
                                     C.byref(push) if push is not None else None, _stream()))
+
+
+def diffusion2d_multistep(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
+                          _dy: float, nsteps: int, grid_barrier: torch.Tensor, barrier_base: int,
+                          push_even: Optional[Push2D] = None, push_odd: Optional[Push2D] = None) -> int:
+    """``nsteps`` fused steps in one cooperative launch (``igg_diffusion2d_multistep``).
+
+    Returns the grid size used (the barrier counter advances by ``nsteps * grid``).  ``push_even`` /
+    ``push_odd`` are the plan descriptors whose destinations are the neighbours' ``T2`` / ``T``."""
+    lib = require()
+    nx, ny = T.shape
+    grid = C.c_int(0)
+    odd = None
+    if push_even is not None:
+        odd = (C.c_void_p * 9)(*[push_odd.peer_dst[k] for k in range(9)])
+    _check(lib.igg_diffusion2d_multistep(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
+                                         int(nsteps), C.byref(push_even) if push_even is not None else None, odd,
+                                         grid_barrier.data_ptr(), int(barrier_base), C.byref(grid), _stream()))
+    return grid.value
 
 
 def diffusion3d_step(T2, T, Cp, lam, dt, _dx, _dy, _dz, mode: int = 0, b_width=(1, 1, 1), variant: str = "tma",

@@ -99,3 +99,17 @@ def test_hide_communication_generic_gpu():
     ref.perf_step(want, T.cpu(), Cp.cpu(), 1.0, 1e-3, 2.0, 3.0)
     igg.VirtualGrid((200, 180), (1, 1), (1, 0)).update_halo([want])
     assert float((T2.cpu() - want).abs().max()) < 1e-13
+
+
+def test_persistent_multistep_matches_oracle_and_counts_one_launch():
+    from rocm_mpi_b200.models.solver import Diffusion2D
+    igg.init_global_grid(128, 128, 1, quiet=True, init_dist=False)
+    s = Diffusion2D(128, 128, mode="persistent")
+    s.begin()
+    n0 = native.launch_count()
+    s.step(101)
+    assert native.launch_count() - n0 == 1            # 101 time steps, one kernel launch
+    s.step(99)
+    s.finish()
+    T_ref, _ = ref.oracle_2d(128, 128, 200, "perf")
+    assert float((s.T.cpu() - T_ref).abs().max()) < 1e-13
