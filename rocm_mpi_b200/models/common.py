@@ -10,6 +10,7 @@ import torch
 from ..ops import reference as ref
 from ..parallel import (coords_g, finalize_global_grid, gather, global_grid, init_global_grid, inner,
                         nx_g, ny_g, nz_g)
+from ..parallel.gather import inner_to_host
 from ..utils.config import DiffusionConfig
 from ..utils.output import output_name, save_heatmap, save_raw
 
@@ -95,7 +96,7 @@ def visualise_2d(s: Setup, T: torch.Tensor, variant: str, res: RunResult) -> Non
     """Strip halo, gather to rank 0, write PNG + raw dump (reference ``scripts/diffusion_2D_ap.jl:45-47``)."""
     cfg = s.cfg
     g = global_grid()
-    T_nh = inner(T).contiguous().cpu()
+    T_nh = inner_to_host(T)
     T_v = None
     if g.me == 0:
         T_v = torch.zeros((cfg.nx - 2) * s.dims[0], (cfg.ny - 2) * s.dims[1], dtype=T.dtype)

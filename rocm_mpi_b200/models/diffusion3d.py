@@ -119,7 +119,8 @@ def diffusion3D(cfg: DiffusionConfig = None, finalize: bool = True) -> RunResult
     res = RunResult("3D", me, nprocs, dims, nt, wtime=wtime, t_eff=T_eff, T_local=s.T,
                     launches=native.launch_count() - n0)
     if cfg.do_vis:
-        T_nh = inner(s.T).contiguous().cpu()
+        from ..parallel.gather import inner_to_host
+        T_nh = inner_to_host(s.T)
         T_v = None
         if me == 0:
             T_v = torch.zeros(tuple((n - 2) * d for n, d in zip(s.shape, dims)), dtype=torch.float64)

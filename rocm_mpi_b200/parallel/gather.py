@@ -15,7 +15,7 @@ import torch
 from .grid import global_grid
 from .topology import cart_coords
 
-__all__ = ["gather", "inner", "gather_interior"]
+__all__ = ["gather", "inner", "inner_to_host", "gather_interior"]
 
 
 def inner(A: torch.Tensor) -> torch.Tensor:
@@ -51,10 +51,26 @@ def gather(A_local: torch.Tensor, A_global: Optional[torch.Tensor], root: int = 
         A_global[sl].copy_(blk)
 
 
+def inner_to_host(A: torch.Tensor) -> torch.Tensor:
+    """Halo-free interior of ``A`` as a contiguous host tensor.
+
+    Restates ``Array(T[2:end-1,2:end-1])`` (reference ``scripts/diffusion_2D_ap.jl:45``): on CUDA the strided
+    interior is compacted by the native ``extract_inner`` kernel and copied into pinned host memory."""
+    if A.is_cuda and A.dtype == torch.float64 and A.is_contiguous():
+        from ..ops import native
+        if native.available():
+            dev = native.extract_inner(A)
+            host = torch.empty(dev.shape, dtype=dev.dtype, pin_memory=True)
+            host.copy_(dev, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return host
+    return inner(A).contiguous().cpu()
+
+
 def gather_interior(A: torch.Tensor, root: int = 0) -> Optional[torch.Tensor]:
     """Convenience: strip the halo, gather, and return the global array on the root."""
     g = global_grid()
-    blk = inner(A)
+    blk = inner_to_host(A)
     out = None
     if g.me == root:
         out = torch.zeros(tuple(blk.shape[d] * g.dims[d] for d in range(blk.dim())),

@@ -30,3 +30,11 @@ def test_apps_multi_gpu(nprocs, tmp_path):
         pytest.skip(f"needs {nprocs} GPUs")
     outs = run_workers("apps_multi_gpu.py", nprocs, (str(tmp_path), nprocs), timeout=900)
     assert all("ok" in o for o in outs)
+
+
+@pytest.mark.parametrize("nprocs,args", [(2, (34, 66, 0, 0, 600)), (2, (20, 34, 1, 1, 400)), (8, (18, 34, 1, 0, 400))])
+def test_flag_protocol_stress_small_grids(nprocs, args):
+    if _ngpu() < nprocs:
+        pytest.skip(f"needs {nprocs} GPUs")
+    outs = run_workers("stress_multi_gpu.py", nprocs, args, timeout=600)
+    assert all("ok" in o for o in outs)
