@@ -5,9 +5,12 @@
 // the boundary frame are scheduled first, edge cells are pushed to the up-to-26 neighbours through
 // peer pointers, modes 0/1/2 = all / frame / inside-the-frame.
 //
-//  * variant 1: persistent kernel, 3-D TMA boxes (8 x 8 x 64 cells + halo) through a 2-stage
-//    mbarrier ring, computed from shared memory;
-//  * variant 0: direct global loads, marching along x with a register window.
+//  * variant 1: persistent, warp-specialised 2.5-D kernel.  A work item is a column of 32 x 128 (y x z)
+//    cells marched along x for up to 32 planes; a producer warp streams the T planes (34 x 132 doubles,
+//    one-cell halo, TMA zero fill at array edges) through a 4-slot ring and the Cp planes through a
+//    2-slot ring; 16 consumer warps compute plane x from the three resident T planes x-1, x, x+1 and
+//    hand the oldest plane back.  Every T plane is read once per column (halo overhead only in y, z).
+//  * variant 0: direct global loads, 8 x 8 x 64 tiles, marching along x with a register window.
 // Layout: T[ix][iy][iz], iz contiguous.
 #include <string.h>
 
@@ -16,16 +19,17 @@
 namespace {
 using namespace igg;
 
-constexpr int TX = 8, TY = 8, TZ = 64;       // tile cells
-// The TMA box must start on a 16-byte boundary (even z for fp64): it starts at z0-2 and is TZ+4 wide,
-// so cell (x,y,z) of a tile sits at smem [(x-x0+1)*PY + (y-y0+1)]*PZ + (z-z0+2).
-constexpr int PZ = TZ + 4, PY = TY + 2, PX = TX + 2;
-constexpr int T3_BYTES = PX * PY * PZ * 8;                        // 54400
-constexpr int T3_PAD = (T3_BYTES + 127) / 128 * 128;              // 54400
-constexpr int C3_BYTES = TX * TY * TZ * 8;                        // 32768
-constexpr int STAGE3_BYTES = T3_PAD + C3_BYTES;                   // 87168
-constexpr int STAGES3_USED = 2;                                   // 3 stages would exceed 227 KB
-constexpr int SMEM3_USED = STAGES3_USED * STAGE3_BYTES + 64;      // 174400
+constexpr int TX = 8, TY = 8, TZ = 64;       // tile cells of the direct kernel
+// 2.5-D TMA kernel: plane tile PTY x PTZ, marched over CX planes.  The TMA box must start on a 16-byte
+// boundary (even z for fp64): it starts at z0-2 and is PTZ+4 wide, so cell (y,z) of a plane tile sits at
+// smem row y-y0+1, column z-z0+2.
+constexpr int CX = 32, PTY = 32, PTZ = 128;
+constexpr int PP = PTZ + 4;                                        // smem pitch of a T plane (doubles)
+constexpr int TPL_BYTES = (PTY + 2) * PP * 8;                      // 35904
+constexpr int TPL_PAD = (TPL_BYTES + 127) / 128 * 128;             // 35968
+constexpr int CPL_BYTES = PTY * PTZ * 8;                           // 32768
+constexpr int NT = 4, NC = 2;                                      // ring depths (T planes, Cp planes)
+constexpr int SMEM3_BYTES = NT * TPL_PAD + NC * CPL_BYTES + 128;   // 209536
 
 struct Seg3 {
     int i0, j0, k0, ni, nj, nk, start;
@@ -88,21 +92,35 @@ __device__ __forceinline__ bool writes(const Params3& p, int x, int y, int z) {
     return w;
 }
 
-// ---- variant 1: TMA --------------------------------------------------------------------------------
-// 256 threads: 32 z-pairs x 8 y; each thread marches the 8 x-planes of the tile.
-__global__ void __launch_bounds__(256, 1)
+// ---- variant 1: 2.5-D TMA kernel ----------------------------------------------------------------------
+__device__ __forceinline__ void mbar_arrive3(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void consumer_sync3(int nthreads) {
+    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
+}
+
+constexpr int RPT3 = 4;                                   // y rows per consumer thread
+constexpr int CONS3 = (PTZ / 2) * (PTY / RPT3);           // 512 consumer threads
+constexpr int NCW3 = CONS3 / 32;
+
+__global__ void __launch_bounds__(CONS3 + 32, 1)
 diff3d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapCp,
                   const __grid_constant__ Params3 p) {
     extern __shared__ __align__(128) unsigned char smem[];
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES3_USED * STAGE3_BYTES);
+    unsigned char* ringT = smem;
+    unsigned char* ringC = smem + NT * TPL_PAD;
+    uint64_t* fullT = reinterpret_cast<uint64_t*>(smem + NT * TPL_PAD + NC * CPL_BYTES);
+    uint64_t* emptyT = fullT + NT;
+    uint64_t* fullC = emptyT + NT;
+    uint64_t* emptyC = fullC + NC;
     const int tid = threadIdx.x;
     const int first = blockIdx.x;
     const int n_my = first < p.ts.ntiles ? (p.ts.ntiles - first + gridDim.x - 1) / gridDim.x : 0;
     if (tid == 0) {
-        for (int s = 0; s < STAGES3_USED; ++s) mbar_init(&full[s], 1);
+        for (int s = 0; s < NT; ++s) { mbar_init(&fullT[s], 1); mbar_init(&emptyT[s], NCW3); }
+        for (int s = 0; s < NC; ++s) { mbar_init(&fullC[s], 1); mbar_init(&emptyC[s], NCW3); }
         fence_mbar_init();
-        tma_prefetch_desc(&mapT);
-        tma_prefetch_desc(&mapCp);
     }
     __syncthreads();
 
@@ -111,69 +129,122 @@ diff3d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
         hi[0] = i == p.t_hi[0] && p.side_nb[0][1]; hi[1] = j == p.t_hi[1] && p.side_nb[1][1];
         hi[2] = k == p.t_hi[2] && p.side_nb[2][1];
     };
-    auto issue = [&](int q) {
-        int i, j, k;
-        tile_of3(p.ts, first + q * gridDim.x, i, j, k);
-        if (p.has_push) {
-            bool lo[3], hi[3];
-            flags_of(i, j, k, lo, hi);
-            if (wait_faces_3d(p.push, lo, hi)) fence_proxy_async();
-        }
-        const int s = q % STAGES3_USED;
-        unsigned char* st = smem + s * STAGE3_BYTES;
-        mbar_arrive_expect_tx(&full[s], T3_BYTES + C3_BYTES);
-        tma_load_3d(st, &mapT, &full[s], k * TZ - 2, j * TY - 1, i * TX - 1);
-        tma_load_3d(st + T3_PAD, &mapCp, &full[s], k * TZ, j * TY, i * TX);
-    };
-    if (tid == 0)
-        for (int q = 0; q < STAGES3_USED - 1 && q < n_my; ++q) issue(q);
 
-    const int zp = tid % (TZ / 2);   // z pair
-    const int yy = tid / (TZ / 2);   // y row in tile
-    for (int q = 0; q < n_my; ++q) {
-        if (tid == 0 && q + STAGES3_USED - 1 < n_my) issue(q + STAGES3_USED - 1);
+    if (tid >= CONS3) {
+        // ===== producer: T planes xa-1 .. xb and Cp planes xa .. xb-1 of every work item ==================
+        if (tid == CONS3) {
+            tma_prefetch_desc(&mapT);
+            tma_prefetch_desc(&mapCp);
+            unsigned tq = 0, cq = 0;                        // planes issued so far (ring positions)
+            auto issue_T = [&](int x, int j, int k) {
+                const unsigned s = tq % NT;
+                if (tq >= NT) mbar_wait(&emptyT[s], ((tq / NT) - 1) & 1);
+                mbar_arrive_expect_tx(&fullT[s], TPL_BYTES);
+                tma_load_3d(ringT + s * TPL_PAD, &mapT, &fullT[s], k * PTZ - 2, j * PTY - 1, x);
+                ++tq;
+            };
+            auto issue_C = [&](int x, int j, int k) {
+                const unsigned s = cq % NC;
+                if (cq >= NC) mbar_wait(&emptyC[s], ((cq / NC) - 1) & 1);
+                mbar_arrive_expect_tx(&fullC[s], CPL_BYTES);
+                tma_load_3d(ringC + s * CPL_BYTES, &mapCp, &fullC[s], k * PTZ, j * PTY, x);
+                ++cq;
+            };
+            for (int it = 0; it < n_my; ++it) {
+                int i, j, k;
+                tile_of3(p.ts, first + it * gridDim.x, i, j, k);
+                if (p.has_push) {
+                    bool lo[3], hi[3];
+                    flags_of(i, j, k, lo, hi);
+                    if (wait_faces_3d(p.push, lo, hi)) fence_proxy_async();
+                }
+                const int xa = i * CX, n = min(CX, p.nx - xa);
+                issue_T(xa - 1, j, k);
+                issue_T(xa, j, k);
+                for (int m = 0; m < n; ++m) {
+                    issue_T(xa + m + 1, j, k);
+                    issue_C(xa + m, j, k);
+                }
+            }
+        }
+        return;
+    }
+
+    // ===== consumers ====================================================================================
+    const int zp = tid % (PTZ / 2);       // z pair
+    const int rg = tid / (PTZ / 2);       // row group (RPT3 rows)
+    unsigned tq = 0, cq = 0;              // ring position of the item's first T plane / Cp plane
+    for (int it = 0; it < n_my; ++it) {
         int i, j, k;
-        tile_of3(p.ts, first + q * gridDim.x, i, j, k);
-        const int s = q % STAGES3_USED;
-        mbar_wait(&full[s], (q / STAGES3_USED) & 1);
+        tile_of3(p.ts, first + it * gridDim.x, i, j, k);
         bool lo[3], hi[3];
         flags_of(i, j, k, lo, hi);
         const bool edge_tile = p.has_push && (lo[0] || lo[1] || lo[2] || hi[0] || hi[1] || hi[2]);
-        // this thread: y row yy, z cells 2*zp, 2*zp+1 -> smem columns 2*zp+2, 2*zp+3 (aligned pair)
-        const double* sT = reinterpret_cast<const double*>(smem + s * STAGE3_BYTES) + (size_t)(yy + 1) * PZ + 2 * zp + 2;
-        const double* sC = reinterpret_cast<const double*>(smem + s * STAGE3_BYTES + T3_PAD) + (size_t)yy * TZ + 2 * zp;
-        const int gy = j * TY + yy, gz = k * TZ + 2 * zp;
-        // window over x: centre pairs of planes x-1 (um), x (c), x+1 (d)
-        double2 um = *reinterpret_cast<const double2*>(sT);
-        double2 c = *reinterpret_cast<const double2*>(sT + PY * PZ);
+        const int xa = i * CX, n = min(CX, p.nx - xa);
+        const int gz = k * PTZ + 2 * zp, gyb = j * PTY + rg * RPT3;
+        // planes q = 0 (x-1) and q = 1 (x) of the first compute plane
+        mbar_wait(&fullT[tq % NT], (tq / NT) & 1);
+        mbar_wait(&fullT[(tq + 1) % NT], ((tq + 1) / NT) & 1);
+        for (int m = 0; m < n; ++m) {
+            const unsigned q0 = tq + m, q1 = q0 + 1, q2 = q0 + 2, qc = cq + m;
+            mbar_wait(&fullT[q2 % NT], (q2 / NT) & 1);
+            mbar_wait(&fullC[qc % NC], (qc / NC) & 1);
+            const int gx = xa + m;
+            if (gx >= 1 && gx <= p.nx - 2) {
+                const size_t off = (size_t)(rg * RPT3) * PP + 2 * zp + 2;   // row above the thread's first row
+                const double* P0 = reinterpret_cast<const double*>(ringT + (q0 % NT) * TPL_PAD) + off;
+                const double* P1 = reinterpret_cast<const double*>(ringT + (q1 % NT) * TPL_PAD) + off;
+                const double* P2 = reinterpret_cast<const double*>(ringT + (q2 % NT) * TPL_PAD) + off;
+                const double* sC = reinterpret_cast<const double*>(ringC + (qc % NC) * CPL_BYTES) +
+                                   (size_t)(rg * RPT3) * PTZ + 2 * zp;
+                // 3-row window over y inside the centre plane
+                double2 a = *reinterpret_cast<const double2*>(P1);
+                double2 b = *reinterpret_cast<const double2*>(P1 + PP);
 #pragma unroll
-        for (int r = 0; r < TX; ++r) {
-            const double* pl = sT + (size_t)(r + 1) * PY * PZ;            // centre plane
-            const double2 d = *reinterpret_cast<const double2*>(pl + PY * PZ);
-            const double2 ym = *reinterpret_cast<const double2*>(pl - PZ);
-            const double2 yp = *reinterpret_cast<const double2*>(pl + PZ);
-            const double zl = pl[-1], zr = pl[2];
-            const double2 cc = *reinterpret_cast<const double2*>(sC + (size_t)r * TY * TZ);
-            const int gx = i * TX + r;
-            const double vA = update_cell3(c.x, um.x, d.x, ym.x, yp.x, zl, c.y, cc.x, p);
-            const double vB = update_cell3(c.y, um.y, d.y, ym.y, yp.y, c.x, zr, cc.y, p);
-            const bool wA = writes(p, gx, gy, gz), wB = writes(p, gx, gy, gz + 1);
-            double* out = p.T2 + ((size_t)gx * p.ny + gy) * p.nz + gz;
-            if (wA && wB) {
-                st_cs_f64x2(out, vA, vB);
-            } else {
-                if (wA) st_cs_f64(out, vA);
-                if (wB) st_cs_f64(out + 1, vB);
+                for (int r = 0; r < RPT3; ++r) {
+                    const double2 c = *reinterpret_cast<const double2*>(P1 + (r + 2) * PP);
+                    const double zl = P1[(r + 1) * PP - 1], zr = P1[(r + 1) * PP + 2];
+                    const double2 xm = *reinterpret_cast<const double2*>(P0 + (r + 1) * PP);
+                    const double2 xp = *reinterpret_cast<const double2*>(P2 + (r + 1) * PP);
+                    const double2 cc = *reinterpret_cast<const double2*>(sC + r * PTZ);
+                    const int gy = gyb + r;
+                    const double vA = update_cell3(b.x, xm.x, xp.x, a.x, c.x, zl, b.y, cc.x, p);
+                    const double vB = update_cell3(b.y, xm.y, xp.y, a.y, c.y, b.x, zr, cc.y, p);
+                    const bool wA = writes(p, gx, gy, gz), wB = writes(p, gx, gy, gz + 1);
+                    double* out = p.T2 + ((size_t)gx * p.ny + gy) * p.nz + gz;
+                    if (wA && wB) {
+                        st_cs_f64x2(out, vA, vB);
+                    } else {
+                        if (wA) st_cs_f64(out, vA);
+                        if (wB) st_cs_f64(out + 1, vB);
+                    }
+                    if (edge_tile) {
+                        if (wA) push_cell_3d(p.push, p.nx, p.ny, p.nz, gx, gy, gz, vA);
+                        if (wB) push_cell_3d(p.push, p.nx, p.ny, p.nz, gx, gy, gz + 1, vB);
+                    }
+                    a = b;
+                    b = c;
+                }
             }
-            if (edge_tile) {
-                if (wA) push_cell_3d(p.push, p.nx, p.ny, p.nz, gx, gy, gz, vA);
-                if (wB) push_cell_3d(p.push, p.nx, p.ny, p.nz, gx, gy, gz + 1, vB);
+            // plane x-1 and this Cp plane are no longer needed
+            __syncwarp();
+            if ((tid & 31) == 0) {
+                mbar_arrive3(&emptyT[q0 % NT]);
+                mbar_arrive3(&emptyC[qc % NC]);
             }
-            um = c;
-            c = d;
         }
-        __syncthreads();
-        if (edge_tile && tid == 0) signal_edges_3d(p.push, p.edge_tiles, lo, hi);
+        // the last two T planes of the column
+        __syncwarp();
+        if ((tid & 31) == 0) {
+            mbar_arrive3(&emptyT[(tq + n) % NT]);
+            mbar_arrive3(&emptyT[(tq + n + 1) % NT]);
+        }
+        tq += n + 2;
+        cq += n;
+        if (edge_tile) {
+            consumer_sync3(CONS3);
+            if (tid == 0) signal_edges_3d(p.push, p.edge_tiles, lo, hi);
+        }
     }
 }
 
@@ -233,8 +304,7 @@ static void add_seg3(TileSet3& ts, int i0, int i1, int j0, int j1, int k0, int k
     ts.ntiles += s.ni * s.nj * s.nk;
 }
 
-static void build_tiles3(TileSet3& ts, const int n[3], int mode, const int bw[3]) {
-    const int tsz[3] = {TX, TY, TZ};
+static void build_tiles3(TileSet3& ts, const int n[3], int mode, const int bw[3], const int tsz[3]) {
     ts.nseg = 0;
     ts.ntiles = 0;
     int nt[3], a0[3], a1[3];
@@ -246,7 +316,7 @@ static void build_tiles3(TileSet3& ts, const int n[3], int mode, const int bw[3]
             hi[d] = n[d] - 2 - bw[d];
             if (hi[d] < lo[d]) return;
         }
-        add_seg3(ts, lo[0] / TX, hi[0] / TX, lo[1] / TY, hi[1] / TY, lo[2] / TZ, hi[2] / TZ);
+        add_seg3(ts, lo[0] / tsz[0], hi[0] / tsz[0], lo[1] / tsz[1], hi[1] / tsz[1], lo[2] / tsz[2], hi[2] / tsz[2]);
         return;
     }
     for (int d = 0; d < 3; ++d) {
@@ -291,13 +361,14 @@ extern "C" int igg_diffusion3d_step(const double* T, double* T2, const double* C
     p.mode = mode;
     p.bw[0] = bwx < 1 ? 1 : bwx; p.bw[1] = bwy < 1 ? 1 : bwy; p.bw[2] = bwz < 1 ? 1 : bwz;
     const int n[3] = {nx, ny, nz};
-    const int tsz[3] = {TX, TY, TZ};
+    const int tsz_direct[3] = {TX, TY, TZ}, tsz_tma[3] = {CX, PTY, PTZ};
+    const int* tsz = variant == 1 ? tsz_tma : tsz_direct;
     int nt[3];
     for (int d = 0; d < 3; ++d) {
         p.t_hi[d] = (n[d] - 2) / tsz[d];
         nt[d] = p.t_hi[d] + 1;
     }
-    build_tiles3(p.ts, n, mode, p.bw);
+    build_tiles3(p.ts, n, mode, p.bw, tsz);
     if (p.ts.ntiles == 0) return 0;
     p.has_push = push ? 1 : 0;
     for (int sx = -1; sx <= 1; ++sx)
@@ -328,8 +399,8 @@ extern "C" int igg_diffusion3d_step(const double* T, double* T2, const double* C
         }
         CUtensorMap mT, mC;
         const uint64_t dims[3] = {(uint64_t)nz, (uint64_t)ny, (uint64_t)nx};
-        const uint32_t boxT[3] = {PZ, PY, PX};
-        const uint32_t boxC[3] = {TZ, TY, TX};
+        const uint32_t boxT[3] = {PP, PTY + 2, 1};
+        const uint32_t boxC[3] = {PTZ, PTY, 1};
         int rc = igg::get_tensor_map_f64(T, 3, dims, boxT, &mT);
         if (rc) return rc;
         rc = igg::get_tensor_map_f64(Cp, 3, dims, boxC, &mC);
@@ -337,11 +408,11 @@ extern "C" int igg_diffusion3d_step(const double* T, double* T2, const double* C
         int dev = 0;
         IGG_CUDA_OK(cudaGetDevice(&dev));
         if (dev < 0 || dev >= 64 || !g_attr3_set[dev]) {
-            IGG_CUDA_OK(cudaFuncSetAttribute(diff3d_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM3_USED));
+            IGG_CUDA_OK(cudaFuncSetAttribute(diff3d_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM3_BYTES));
             if (dev >= 0 && dev < 64) g_attr3_set[dev] = true;
         }
         const int grid = p.ts.ntiles < igg::sm_count() ? p.ts.ntiles : igg::sm_count();
-        diff3d_tma_kernel<<<grid, 256, SMEM3_USED, st>>>(mT, mC, p);
+        diff3d_tma_kernel<<<grid, CONS3 + 32, SMEM3_BYTES, st>>>(mT, mC, p);
         IGG_LAUNCH_CHECK();
     } else {
         diff3d_direct_kernel<<<p.ts.ntiles, 256, 0, st>>>(p);
