@@ -661,3 +661,30 @@ extern "C" int igg_diffusion2d_multistep(double* T, double* T2, const double* Cp
     IGG_LAUNCH_CHECK();
     return 0;
 }
+
+// Native time loop: `nsteps` launches of igg_diffusion2d_step with the buffers (and push descriptors)
+// alternating, issued back to back from C++ so that small grids are not bound by per-step interpreter
+// overhead (the reference's loop: scripts/diffusion_2D_perf.jl:47-52 without the host wait).
+extern "C" int igg_diffusion2d_run(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
+                                   double _dx, double _dy, int bwx, int bwy, int variant, int nsteps,
+                                   const igg_push2d* push_even, const igg_push2d* push_odd, void* stream) {
+    IGG_REQUIRE(nsteps >= 0, "igg_diffusion2d_run: nsteps must be >= 0");
+    IGG_REQUIRE((push_even == nullptr) == (push_odd == nullptr), "igg_diffusion2d_run: give both descriptors or none");
+    igg_push2d pe, po;
+    if (push_even) {
+        pe = *push_even;
+        po = *push_odd;
+    }
+    for (int s = 0; s < nsteps; ++s) {
+        const bool even = (s & 1) == 0;
+        igg_push2d* ps = nullptr;
+        if (push_even) {
+            ps = even ? &pe : &po;
+            ps->epoch = push_even->epoch + (uint64_t)s;
+        }
+        const int rc = igg_diffusion2d_step(even ? T : T2, even ? T2 : T, Cp, nx, ny, lam, dt, _dx, _dy, nullptr, 0,
+                                            bwx, bwy, variant, ps, stream);
+        if (rc) return rc;
+    }
+    return 0;
+}

@@ -75,6 +75,14 @@ int igg_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, 
                          double dt, double _dx, double _dy, const igg_step_opts* opts, int mode, int bwx,
                          int bwy, int variant, const igg_push2d* push, void* stream);
 
+/* `nsteps` back-to-back launches of igg_diffusion2d_step (mode 0) from a native loop; step s reads T
+ * (s even) or T2 (s odd).  `push_even` pushes into the neighbours' T2 and carries the epoch of step 0,
+ * `push_odd` pushes into the neighbours' T; both NULL = no communication.
+ * (reference loop: scripts/diffusion_2D_perf.jl:47-52) */
+int igg_diffusion2d_run(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt, double _dx,
+                        double _dy, int bwx, int bwy, int variant, int nsteps, const igg_push2d* push_even,
+                        const igg_push2d* push_odd, void* stream);
+
 /* `nsteps` fused steps in ONE cooperative launch, for local grids so small that a step is pure launch
  * latency (reference loop: scripts/diffusion_2D_kp.jl:87-92 at 128 x 128; no reference counterpart for the
  * single-launch form).  Step s reads T (s even) or T2 (s odd) and writes the other; after the call the

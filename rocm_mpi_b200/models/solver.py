@@ -159,6 +159,19 @@ class Diffusion2D:
                 self.T, self.T2 = self.T2, self.T
             self.steps_done += n
             return
+        if self.mode == "fused" and n > 1 and dev_params is None and diag_out is None:
+            # native time loop: same launches, no per-step interpreter overhead
+            pe = po = None
+            if self.plan.fab.neighbors:
+                pe, po = self.plan._desc[self.T2.data_ptr()], self.plan._desc[self.T.data_ptr()]
+                pe.epoch = self.plan.epoch + 1
+                self.plan.epoch += n
+            native.diffusion2d_run(self.T, self.T2, self.Cp, self.lam, self.dt, self._dx, self._dy, n,
+                                   b_width=self.b_width, variant=self.variant, push_even=pe, push_odd=po)
+            if n % 2:
+                self.T, self.T2 = self.T2, self.T
+            self.steps_done += n
+            return
         for _ in range(n):
             if self.mode == "fused":
                 self._kernel(0, self.plan.next(self.T2), dev_params, diag_out)

@@ -67,6 +67,7 @@ def _declare(lib) -> None:
         "igg_launch_count": ([], C.c_ulonglong),
         "igg_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d, C.POINTER(StepOpts), i, i, i, i,
                                  C.POINTER(Push2D), vp], i),
+        "igg_diffusion2d_run": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, i, C.POINTER(Push2D), C.POINTER(Push2D), vp], i),
         "igg_diffusion2d_multistep": ([vp, vp, vp, i, i, d, d, d, d, i, C.POINTER(Push2D), C.POINTER(vp), vp,
                                       C.c_ulonglong, C.POINTER(i), vp], i),
         "igg_flux2d": ([vp, vp, vp, i, i, d, d, d, vp], i),
@@ -194,6 +195,19 @@ def diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: f
                                     C.byref(opts) if opts is not None else None,
                                     mode, int(b_width[0]), int(b_width[1]), VARIANTS[variant],
                                     C.byref(push) if push is not None else None, _stream()))
+
+
+def diffusion2d_run(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float, _dy: float,
+                    nsteps: int, b_width: Sequence[int] = (1, 1), variant: str = "tma",
+                    push_even: Optional[Push2D] = None, push_odd: Optional[Push2D] = None) -> None:
+    """``nsteps`` fused steps launched from the native loop (``igg_diffusion2d_run``); the result is in ``T2``
+    if ``nsteps`` is odd, else in ``T``."""
+    lib = require()
+    nx, ny = T.shape
+    _check(lib.igg_diffusion2d_run(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
+                                   int(b_width[0]), int(b_width[1]), VARIANTS[variant], int(nsteps),
+                                   C.byref(push_even) if push_even is not None else None,
+                                   C.byref(push_odd) if push_odd is not None else None, _stream()))
 
 
 def diffusion2d_multistep(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
