@@ -7,6 +7,7 @@ Compares, device-timed and max over ranks:
 * ``kp-nccl``     three kernels + pack / NCCL p2p / unpack per step (the reference's structure, kp.jl:87-92)
 * ``fused``       one fused kernel per step with in-kernel halo push
 * ``persistent``  ONE cooperative launch for all steps (in-kernel grid barrier + halo push)
+* ``resident``    ONE cluster launch, field resident in distributed shared memory, cluster barriers
 
 Run:  ``torchrun --nproc-per-node 8 benchmarks/small_grid_latency.py --nx 65 --ny 128 --dimx 4 --dimy 2``
 """
@@ -51,7 +52,7 @@ def main() -> int:
     variant = "tma" if a.ny % 2 == 0 else "direct"
     for name, kw in (("plain-nccl", dict(mode="plain", variant=variant, transport="nccl")),
                      ("fused", dict(mode="fused", variant=variant)),
-                     ("persistent", dict(mode="persistent"))):
+                     ("persistent", dict(mode="persistent")), ("resident", dict(mode="resident"))):
         s = Diffusion2D(a.nx, a.ny, **kw)
         s.begin()
         s.step(20)

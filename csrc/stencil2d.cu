@@ -688,3 +688,26 @@ extern "C" int igg_diffusion2d_run(double* T, double* T2, const double* Cp, int 
     }
     return 0;
 }
+
+// One end-to-end controlled step, entirely from native code: parameters travel host(pinned) -> device, the
+// fused step runs (reading them from device memory and producing the in-kernel {max, sum} diagnostic), the
+// diagnostic travels device -> host(pinned), and the call returns when it has arrived.  This is what a host
+// control loop (adaptive time stepping, monitoring) executes per step.
+extern "C" int igg_diffusion2d_step_controlled(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                               const double* params_host_pinned, double* params_dev,
+                                               double* diag_dev, void* diag_scratch, double* diag_host_pinned,
+                                               int bwx, int bwy, const igg_push2d* push, void* stream) {
+    IGG_REQUIRE(params_host_pinned && params_dev && diag_dev && diag_scratch && diag_host_pinned,
+                "igg_diffusion2d_step_controlled: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    IGG_CUDA_OK(cudaMemcpyAsync(params_dev, params_host_pinned, 4 * sizeof(double), cudaMemcpyHostToDevice, st));
+    igg_step_opts o;
+    o.dev_params = params_dev;
+    o.diag_out = diag_dev;
+    o.diag_scratch = diag_scratch;
+    const int rc = igg_diffusion2d_step(T, T2, Cp, nx, ny, 0.0, 0.0, 0.0, 0.0, &o, 0, bwx, bwy, 1, push, stream);
+    if (rc) return rc;
+    IGG_CUDA_OK(cudaMemcpyAsync(diag_host_pinned, diag_dev, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    IGG_CUDA_OK(cudaStreamSynchronize(st));
+    return 0;
+}

@@ -75,6 +75,15 @@ int igg_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, 
                          double dt, double _dx, double _dy, const igg_step_opts* opts, int mode, int bwx,
                          int bwy, int variant, const igg_push2d* push, void* stream);
 
+/* One end-to-end step of a host control loop: H2D copy of {lam, dt, _dx, _dy} (32 B) from pinned host
+ * memory, fused step (TMA variant, mode 0) reading them from `params_dev`, in-kernel {max, sum} diagnostic,
+ * D2H copy of the diagnostic (16 B) into pinned host memory, stream synchronised on return
+ * (the per-step monitoring of reference scripts/diffusion_2D_perf_hide.jl:115, done every step). */
+int igg_diffusion2d_step_controlled(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                    const double* params_host_pinned, double* params_dev, double* diag_dev,
+                                    void* diag_scratch, double* diag_host_pinned, int bwx, int bwy,
+                                    const igg_push2d* push, void* stream);
+
 /* `nsteps` back-to-back launches of igg_diffusion2d_step (mode 0) from a native loop; step s reads T
  * (s even) or T2 (s odd).  `push_even` pushes into the neighbours' T2 and carries the epoch of step 0,
  * `push_odd` pushes into the neighbours' T; both NULL = no communication.
@@ -94,6 +103,20 @@ int igg_diffusion2d_multistep(double* T, double* T2, const double* Cp, int nx, i
                               double _dx, double _dy, int nsteps, const igg_push2d* push_even,
                               double* const* peer_dst_odd, unsigned long long* grid_barrier,
                               unsigned long long grid_barrier_base, int* grid_size_out, void* stream);
+
+/* `nsteps` steps with the whole local field resident in the shared memory of ONE thread-block cluster
+ * (<= 16 CTAs): rows shared between CTAs are read through distributed shared memory, steps are separated by
+ * cluster barriers, domain-edge cells are pushed to the neighbours' global arrays and announced with per-CTA
+ * epoch flags.  No reference counterpart (its small runs, scripts/diffusion_2D_kp.jl:87-92, pay 3 launches +
+ * host waits + MPI per step).  IGG_ERR_UNSUPPORTED if the field does not fit (use igg_diffusion2d_multistep).
+ * Result in T2 if nsteps is odd, else in T.  Tables are indexed [(ox+1)*3 + (oy+1)]; `peer_flags[o]` is the
+ * base of the flag region (>= 9*16+1 uint64, zero-initialised, fabric memory) of the neighbour at offset o,
+ * `my_flags` mine; `epoch0` is the epoch of step 0 and must grow by nsteps from call to call.  Pass
+ * peer_flags == NULL for a run without communication. */
+int igg_diffusion2d_resident(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
+                             double _dx, double _dy, int nsteps, double* const* peer_T, double* const* peer_T2,
+                             uint64_t* const* peer_flags, uint64_t* my_flags, uint64_t epoch0,
+                             int* cluster_size_out, void* stream);
 
 /* ---- 2-D diffusion, three-kernel form (reference scripts/diffusion_2D_kp.jl:16-54) ------------ */
 int igg_flux2d(double* qx, double* qy, const double* T, int nx, int ny, double lam, double _dx,

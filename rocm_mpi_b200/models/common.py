@@ -14,7 +14,7 @@ from ..parallel.gather import inner_to_host
 from ..utils.config import DiffusionConfig
 from ..utils.output import output_name, save_heatmap, save_raw
 
-__all__ = ["Setup", "setup_2d", "initial_condition_2d", "visualise_2d", "RunResult", "log0"]
+__all__ = ["Setup", "setup_2d", "initial_condition_2d", "visualise_2d", "RunResult", "log0", "detach_local"]
 
 
 def log0(*a, **k) -> None:
@@ -51,6 +51,15 @@ class RunResult:
     raw: Optional[str] = None
     max_T: Optional[float] = None
     launches: int = 0
+
+
+def detach_local(res: "RunResult", limit_bytes: int = 64 << 20) -> None:
+    """Before ``finalize_global_grid()`` frees peer-addressable fields: keep a private copy of a small local
+    field in the result, drop a large one (it only aliases fabric memory)."""
+    T = res.T_local
+    if T is None or not T.is_cuda:
+        return
+    res.T_local = T.clone() if T.numel() * T.element_size() <= limit_bytes else None
 
 
 def setup_2d(cfg: DiffusionConfig) -> Setup:

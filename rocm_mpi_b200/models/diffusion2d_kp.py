@@ -28,7 +28,7 @@ from ..parallel import finalize_global_grid, global_grid, update_halo
 from ..parallel.fabric import PushPlan, fabric_zeros, get_fabric
 from ..parallel.halo import default_transport
 from ..utils.config import DiffusionConfig, add_config_args, config_from_args
-from .common import RunResult, initial_condition_2d, log0, setup_2d, visualise_2d
+from .common import detach_local, RunResult, initial_condition_2d, log0, setup_2d, visualise_2d
 
 __all__ = ["diffusion2D_kp", "main"]
 
@@ -97,6 +97,7 @@ def diffusion2D_kp(cfg: DiffusionConfig = None, finalize: bool = True) -> RunRes
     if cfg.do_vis:
         visualise_2d(s, T, "kp", res)
     if finalize:
+        detach_local(res)
         finalize_global_grid()
     return res
 

@@ -21,7 +21,7 @@ from ..ops import native
 from ..parallel import a_eff, finalize_global_grid, global_grid, tic, toc
 from ..utils.config import DiffusionConfig, add_config_args, config_from_args
 from ..utils.profiling import nvtx_range
-from .common import RunResult, log0, setup_2d, visualise_2d
+from .common import detach_local, RunResult, log0, setup_2d, visualise_2d
 from .solver import Diffusion2D
 
 __all__ = ["diffusion2D_perf", "run_timed", "main"]
@@ -72,6 +72,7 @@ def diffusion2D_perf(cfg: DiffusionConfig = None, mode: str = None, variant_name
         visualise_2d(su, s.T, variant_name, res)
         log0("maximum(T_v) = %r" % res.max_T)        # reference scripts/diffusion_2D_perf_hide.jl:115
     if finalize:
+        detach_local(res)
         finalize_global_grid()
     return res
 

@@ -18,7 +18,7 @@ from ..ops import native
 from ..parallel import a_eff, finalize_global_grid, global_grid
 from ..utils.config import DiffusionConfig, add_config_args, config_from_args
 from ..utils.profiling import HostProfile, cuda_profiler_range
-from .common import RunResult, log0, setup_2d
+from .common import detach_local, RunResult, log0, setup_2d
 from .diffusion2d_perf import run_timed
 from .solver import Diffusion2D
 
@@ -53,6 +53,7 @@ def diffusion2D_perf_hide_prof(cfg: DiffusionConfig = None, prof_path: str = "pr
         os.makedirs(os.path.dirname(os.path.abspath(prof_path)), exist_ok=True)
         hp.dump(prof_path)                               # reference :119-121
     if finalize:
+        detach_local(res)
         finalize_global_grid()
     return res
 

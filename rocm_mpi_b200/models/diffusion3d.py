@@ -24,7 +24,7 @@ from ..parallel.fabric import PushPlan, fabric_zeros
 from ..parallel.halo import default_transport
 from ..utils.config import DiffusionConfig, add_config_args, config_from_args
 from ..utils.output import output_name, save_heatmap, save_raw
-from .common import RunResult, log0
+from .common import detach_local, RunResult, log0
 
 __all__ = ["Diffusion3D", "diffusion3D", "main"]
 
@@ -131,6 +131,7 @@ def diffusion3D(cfg: DiffusionConfig = None, finalize: bool = True) -> RunResult
             res.png = save_heatmap(base + ".png", T_v[:, :, T_v.shape[2] // 2], title="3D: mid-plane z slice")
             res.raw, _ = save_raw(base, T_v, {"variant": "3D", "nprocs": nprocs, "dims": list(dims), "nt": nt})
     if finalize:
+        detach_local(res)
         finalize_global_grid()
     return res
 

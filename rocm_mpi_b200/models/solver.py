@@ -12,6 +12,9 @@ offers three ways to advance, all producing the same field:
            join, swap.
 ``persistent``  for small local grids: ``step(n)`` is ONE cooperative launch that runs all ``n`` steps with
            in-kernel grid barriers and the same in-kernel halo pushes (no per-step launch latency).
+``resident``  for grids that fit in the shared memory of one thread-block cluster (up to ~256 x 256): the
+           field stays in shared memory for all ``n`` steps of a ``step(n)`` call; CTAs exchange rows through
+           distributed shared memory and cluster barriers, GPUs through peer stores and per-CTA flags.
 ``plain``  the reference's serial structure (``scripts/diffusion_2D_perf.jl:49-51``): full kernel,
            swap, ``update_halo(T)`` over the chosen transport (``nccl`` = the same-box baseline).
 
@@ -43,8 +46,8 @@ class Diffusion2D:
             raise RuntimeError("Diffusion2D runs on CUDA devices; use models.diffusion2d_ap on CPU")
         if (nx, ny) != tuple(g.nxyz[:2]):
             raise ValueError("nx, ny must be the local sizes given to init_global_grid")
-        if mode not in ("fused", "hide", "plain", "persistent"):
-            raise ValueError("mode must be fused | hide | plain | persistent")
+        if mode not in ("fused", "hide", "plain", "persistent", "resident"):
+            raise ValueError("mode must be fused | hide | plain | persistent | resident")
         native.require()
         self.g = g
         self.nx, self.ny = nx, ny
@@ -56,8 +59,8 @@ class Diffusion2D:
         self.b_width = (int(b_width[0]), int(b_width[1]))
         dev = g.device
         self.transport = transport or default_transport(torch.empty(0, device=dev))
-        self.uses_peer = mode in ("fused", "hide", "persistent") or self.transport == "peer"
-        if mode == "persistent":
+        self.uses_peer = mode in ("fused", "hide", "persistent", "resident") or self.transport == "peer"
+        if mode in ("persistent", "resident"):
             variant = self.variant = "direct"      # the multi-step kernel reads the field through L2 directly
         if variant == "tma" and ny % 2:
             raise ValueError("variant 'tma' needs an even ny (16-byte row pitch); use variant='direct'")
@@ -72,8 +75,12 @@ class Diffusion2D:
         self._init_condition(host_ic)
         self.T2.copy_(self.T)                      # reference scripts/diffusion_2D_perf.jl:36
         self.plan: Optional[PushPlan] = None
-        if mode in ("fused", "hide", "persistent"):
+        if mode in ("fused", "hide", "persistent", "resident"):
             self.plan = PushPlan(self.T, self.T2)
+        self._rflags = None
+        self._repoch = 0
+        if mode == "resident":
+            self._rflags = fabric_zeros((9 * 16 + 16,), torch.int64)      # per-(offset, CTA) epoch flags
         self._gbar = torch.zeros(1, dtype=torch.int64, device=dev)
         self._gbar_base = 0
         self._running = False
@@ -121,6 +128,11 @@ class Diffusion2D:
 
     def finish(self) -> None:
         """Collective: all pushes have landed; after this the halos of ``T`` are valid."""
+        if self._rflags is not None and self._running:
+            torch.cuda.current_stream().synchronize()
+            if int(self._rflags[9 * 16].item()) != 0:
+                self._rflags[9 * 16] = 0
+                raise RuntimeError("a flag wait of the cluster-resident kernel timed out")
         if self._s_hi is not None:
             torch.cuda.current_stream().wait_stream(self._s_hi)
             torch.cuda.current_stream().wait_stream(self._s_lo)
@@ -142,6 +154,26 @@ class Diffusion2D:
             self.begin()
         if diag_out is not None and not self.fused_diag:
             raise ValueError("in-kernel diagnostics need mode='fused' or 'plain' with variant='tma'")
+        if self.mode == "resident":
+            if dev_params is not None or diag_out is not None:
+                raise ValueError("mode='resident' takes its parameters by value and has no in-kernel diagnostic")
+            if n <= 0:
+                return
+            fab = self.plan.fab
+            pT = pT2 = pF = None
+            if fab.neighbors:
+                pT, pT2, pF = [0] * 9, [0] * 9, [0] * 9
+                for (o, r) in fab.neighbors:
+                    k = (o[0] + 1) * 3 + (o[1] + 1)
+                    pT[k], pT2[k] = fab.peer_ptr(self.T, r), fab.peer_ptr(self.T2, r)
+                    pF[k] = fab.peer_ptr(self._rflags, r)
+            native.diffusion2d_resident(self.T, self.T2, self.Cp, self.lam, self.dt, self._dx, self._dy, n, pT, pT2,
+                                        pF, self._rflags.data_ptr(), self._repoch + 1)
+            self._repoch += n
+            if n % 2:
+                self.T, self.T2 = self.T2, self.T
+            self.steps_done += n
+            return
         if self.mode == "persistent":
             if dev_params is not None:
                 raise ValueError("mode='persistent' takes its parameters by value")
@@ -207,6 +239,16 @@ class Diffusion2D:
         p[1] = self.dt if dt is None else dt
         p[2] = self._dx
         p[3] = self._dy
+        if self.mode == "fused" and self.variant == "tma":
+            # the whole step -- H2D 32 B, fused kernel with in-kernel diagnostic, D2H 16 B, sync -- is one
+            # native call
+            if not self._running:
+                self.begin()
+            native.diffusion2d_step_controlled(self.T2, self.T, self.Cp, p, self._params_dev, self._diag_dev,
+                                               self._diag_pin, b_width=self.b_width, push=self.plan.next(self.T2))
+            self.T, self.T2 = self.T2, self.T
+            self.steps_done += 1
+            return float(self._diag_pin[0]), float(self._diag_pin[1])
         self._params_dev.copy_(p, non_blocking=True)                   # H2D, 32 bytes
         if self.fused_diag:
             self.step(1, dev_params=self._params_dev, diag_out=self._diag_dev)   # diagnostic inside the kernel

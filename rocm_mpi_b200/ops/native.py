@@ -67,6 +67,9 @@ def _declare(lib) -> None:
         "igg_launch_count": ([], C.c_ulonglong),
         "igg_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d, C.POINTER(StepOpts), i, i, i, i,
                                  C.POINTER(Push2D), vp], i),
+        "igg_diffusion2d_step_controlled": ([vp, vp, vp, i, i, vp, vp, vp, vp, vp, i, i, C.POINTER(Push2D), vp], i),
+        "igg_diffusion2d_resident": ([vp, vp, vp, i, i, d, d, d, d, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), vp,
+                                     u64, C.POINTER(i), vp], i),
         "igg_diffusion2d_run": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, i, C.POINTER(Push2D), C.POINTER(Push2D), vp], i),
         "igg_diffusion2d_multistep": ([vp, vp, vp, i, i, d, d, d, d, i, C.POINTER(Push2D), C.POINTER(vp), vp,
                                       C.c_ulonglong, C.POINTER(i), vp], i),
@@ -195,6 +198,43 @@ def diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: f
                                     C.byref(opts) if opts is not None else None,
                                     mode, int(b_width[0]), int(b_width[1]), VARIANTS[variant],
                                     C.byref(push) if push is not None else None, _stream()))
+
+
+def diffusion2d_step_controlled(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, params_pin: torch.Tensor,
+                                params_dev: torch.Tensor, diag_dev: torch.Tensor, diag_pin: torch.Tensor,
+                                b_width: Sequence[int] = (1, 1), push: Optional[Push2D] = None) -> None:
+    """One end-to-end controlled step from native code (``igg_diffusion2d_step_controlled``): H2D of the 4
+    parameters, fused step, D2H of ``[max, sum]``; returns after the diagnostic has arrived in ``diag_pin``."""
+    lib = require()
+    nx, ny = T.shape
+    if not (params_pin.is_pinned() and diag_pin.is_pinned()):
+        raise TypeError("params_pin and diag_pin must be pinned host tensors")
+    _check(lib.igg_diffusion2d_step_controlled(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny,
+                                               params_pin.data_ptr(), _f64(params_dev), _f64(diag_dev),
+                                               _reduce_scratch(T.device).data_ptr(), diag_pin.data_ptr(),
+                                               int(b_width[0]), int(b_width[1]),
+                                               C.byref(push) if push is not None else None, _stream()))
+
+
+def diffusion2d_resident(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
+                         _dy: float, nsteps: int, peer_T=None, peer_T2=None, peer_flags=None, my_flags: int = 0,
+                         epoch0: int = 0) -> int:
+    """``nsteps`` steps with the field resident in one thread-block cluster (``igg_diffusion2d_resident``).
+
+    ``peer_T`` / ``peer_T2`` / ``peer_flags``: sequences of 9 raw pointers (0 = no neighbour) indexed
+    ``(ox+1)*3 + (oy+1)``, or ``None`` for a run without communication.  Returns the cluster size used."""
+    lib = require()
+    nx, ny = T.shape
+    csz = C.c_int(0)
+    if peer_flags is None:
+        a = b = f = None
+    else:
+        a = (C.c_void_p * 9)(*[x or None for x in peer_T])
+        b = (C.c_void_p * 9)(*[x or None for x in peer_T2])
+        f = (C.c_void_p * 9)(*[x or None for x in peer_flags])
+    _check(lib.igg_diffusion2d_resident(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
+                                        int(nsteps), a, b, f, my_flags or None, int(epoch0), C.byref(csz), _stream()))
+    return csz.value
 
 
 def diffusion2d_run(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float, _dy: float,

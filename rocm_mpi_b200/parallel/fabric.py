@@ -70,7 +70,8 @@ class Fabric:
             raise RuntimeError("the peer fabric needs CUDA devices")
         self.g = g
         self.lib = native.require()
-        self._owned: List[int] = []                     # pointers from igg_fabric_alloc
+        self._owned: Dict[int, int] = {}                # pointer -> bytes, from igg_fabric_alloc
+        self._handles: Dict[int, Dict[int, bytes]] = {}  # local data_ptr -> {rank: IPC handle it was mapped from}
         self._opened: Dict[bytes, int] = {}             # IPC handle -> mapped base pointer
         self._peer_ptrs: Dict[int, Dict[int, int]] = {}  # local data_ptr -> {rank: peer pointer}
         self._keepalive: List[object] = []
@@ -107,7 +108,7 @@ class Fabric:
         nbytes = max(numel * torch.empty((), dtype=dtype).element_size(), 16)
         ptr = C.c_void_p()
         native._check(self.lib.igg_fabric_alloc(nbytes, C.byref(ptr)))
-        self._owned.append(ptr.value)
+        self._owned[ptr.value] = nbytes
         blk = _DeviceBlock(ptr.value, shape, _TYPESTR[dtype])
         t = torch.as_tensor(blk, device=self.g.device)
         if t.data_ptr() != ptr.value:
@@ -135,10 +136,12 @@ class Fabric:
                                f"segments): {e}") from e
         infos = g.comm.allgather_object((bytes(handle), int(off.value)))
         ptrs = {g.me: key}
+        self._handles[key] = {}
         for r in self.neighbor_ranks:
             if r == g.me:
                 continue
             h, o = infos[r]
+            self._handles[key][r] = h
             base = self._opened.get(h)
             if base is None:
                 out = C.c_void_p()
@@ -187,15 +190,39 @@ class Fabric:
             raise RuntimeError(f"peer flag wait timed out on bank {bank} (word {v & ((1 << 63) - 1)}); "
                                "a neighbour did not reach the matching call")
 
+    def free(self, t: torch.Tensor) -> None:
+        """Collective: unmap ``t`` on every neighbour and release its memory.
+
+        ``t`` (and every view of it) must not be used afterwards: the tensor only aliases the block."""
+        key = t.data_ptr()
+        if key not in self._owned:
+            raise ValueError("tensor was not allocated by this fabric")
+        torch.cuda.synchronize()
+        self.g.comm.barrier()
+        for h in set(self._handles.pop(key, {}).values()):
+            base = self._opened.pop(h, None)
+            if base is not None:
+                self.lib.igg_ipc_close(base)
+        self._peer_ptrs.pop(key, None)
+        self.g.comm.barrier()                       # nobody maps the block any more
+        native._check(self.lib.igg_fabric_free(key))
+        del self._owned[key]
+
     def close(self) -> None:
+        """Collective: unmap all peer memory, then free every block this fabric allocated.
+
+        Tensors obtained from :meth:`zeros` alias those blocks and are invalid from here on."""
         torch.cuda.synchronize()
         self.g.comm.barrier()
         for base in self._opened.values():
             self.lib.igg_ipc_close(base)
         self._opened.clear()
         self._peer_ptrs.clear()
-        # owned blocks stay alive while torch tensors alias them; free them only at process exit
-        # unless nothing references them any more (the tensors are views on raw pointers)
+        self._handles.clear()
+        self.g.comm.barrier()                       # every rank has dropped its mappings
+        for ptr in list(self._owned):
+            self.lib.igg_fabric_free(ptr)
+        self._owned.clear()
         self._keepalive.clear()
 
 

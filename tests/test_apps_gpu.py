@@ -113,3 +113,50 @@ def test_persistent_multistep_matches_oracle_and_counts_one_launch():
     s.finish()
     T_ref, _ = ref.oracle_2d(128, 128, 200, "perf")
     assert float((s.T.cpu() - T_ref).abs().max()) < 1e-13
+
+
+@pytest.mark.parametrize("mode", ["fused", "plain", "hide"])
+def test_step_controlled_end_to_end_values(mode):
+    from rocm_mpi_b200.models.solver import Diffusion2D
+    igg.init_global_grid(200, 260, 1, periodx=1, quiet=True, init_dist=False)
+    s = Diffusion2D(200, 260, mode=mode, variant="tma", transport="peer")
+    ref_s = Diffusion2D(200, 260, mode="plain", variant="direct", transport="peer")
+    s.begin()
+    ref_s.begin()
+    for k in range(4):
+        mx, sm = s.step_controlled(dt=s.dt * (1.0 + 0.1 * k))       # host-chosen parameters take effect
+        ref_s.dt_backup = ref_s.dt
+        ref_s.dt = ref_s.dt_backup * (1.0 + 0.1 * k)
+        ref_s.step(1)
+        ref_s.dt = ref_s.dt_backup
+        inner = ref_s.T[1:-1, 1:-1]
+        assert abs(mx - float(inner.max())) < 1e-13
+        assert abs(sm - float(inner.sum())) < 1e-9 * abs(float(inner.sum())) + 1e-9
+    s.finish()
+    ref_s.finish()
+    assert float((s.T - ref_s.T).abs().max()) < 1e-13
+
+
+@pytest.mark.parametrize("shape", [(128, 128), (65, 128), (254, 254), (33, 70), (17, 40)])
+def test_cluster_resident_kernel_matches_oracle(shape):
+    from rocm_mpi_b200.models.solver import Diffusion2D
+    nx, ny = shape
+    igg.init_global_grid(nx, ny, 1, quiet=True, init_dist=False)
+    s = Diffusion2D(nx, ny, mode="resident")
+    s.begin()
+    n0 = native.launch_count()
+    s.step(61)
+    assert native.launch_count() - n0 == 1
+    s.step(40)
+    s.finish()
+    T_ref, _ = ref.oracle_2d(nx, ny, 101, "perf")
+    assert float((s.T.cpu() - T_ref).abs().max()) < 1e-13
+
+
+def test_cluster_resident_kernel_rejects_large_fields():
+    from rocm_mpi_b200.models.solver import Diffusion2D
+    igg.init_global_grid(1024, 1024, 1, quiet=True, init_dist=False)
+    s = Diffusion2D(1024, 1024, mode="resident")
+    s.begin()
+    with pytest.raises(native.NativeError):
+        s.step(2)

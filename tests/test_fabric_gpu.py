@@ -42,7 +42,7 @@ def test_update_halo_peer_periodic_self(shape, periods):
 
 
 @pytest.mark.parametrize("variant", ["tma", "direct"])
-@pytest.mark.parametrize("mode", ["fused", "hide", "plain", "persistent"])
+@pytest.mark.parametrize("mode", ["fused", "hide", "plain", "persistent", "resident"])
 def test_solver_periodic_self_neighbor(variant, mode):
     from rocm_mpi_b200.models.solver import Diffusion2D
     nx, ny = 96, 260

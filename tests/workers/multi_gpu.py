@@ -32,7 +32,7 @@ get_fabric().check_errors(0)
 gx, gy = igg.nx_g(), igg.ny_g()
 results = {}
 for mode, variant, transport in (("fused", "tma", "peer"), ("fused", "direct", "peer"), ("hide", "tma", "peer"),
-                                 ("plain", "tma", "nccl"), ("plain", "tma", "peer"), ("persistent", "direct", "peer")):
+                                 ("plain", "tma", "nccl"), ("plain", "tma", "peer"), ("persistent", "direct", "peer"), ("resident", "direct", "peer")):
     s = Diffusion2D(nx, ny, mode=mode, variant=variant, transport=transport, b_width=(8, 4))
     T0 = s.T.cpu().clone()
     s.begin()
