@@ -98,6 +98,8 @@ class ClockSampler:
 def main() -> int:
     a = parse_args()
     if a.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:      # under torchrun: one line, from rank 0
+            return 0
         print(json.dumps({"impl": "reference", "unavailable":
                           "reference is Julia scripts on AMDGPU.jl/ROCm-aware MPI (no Python package, no CUDA "
                           "path); julia/MPI/ROCm are not in this image and cannot be installed offline"}))

@@ -708,6 +708,20 @@ extern "C" int igg_diffusion2d_step_controlled(const double* T, double* T2, cons
     const int rc = igg_diffusion2d_step(T, T2, Cp, nx, ny, 0.0, 0.0, 0.0, 0.0, &o, 0, bwx, bwy, 1, push, stream);
     if (rc) return rc;
     IGG_CUDA_OK(cudaMemcpyAsync(diag_host_pinned, diag_dev, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
-    IGG_CUDA_OK(cudaStreamSynchronize(st));
+    // Wait for the diagnostic.  Polling an event keeps the host thread on the CPU (no blocking-sync wake-up
+    // latency), which matters when this call is made once per ~1 ms step.
+    static int spin = -1;
+    if (spin < 0) spin = env_int("IGG_E2E_SPIN", 1);
+    if (spin) {
+        static thread_local cudaEvent_t ev = nullptr;
+        if (!ev) IGG_CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        IGG_CUDA_OK(cudaEventRecord(ev, st));
+        cudaError_t q;
+        while ((q = cudaEventQuery(ev)) == cudaErrorNotReady) {
+        }
+        IGG_CUDA_OK(q);
+    } else {
+        IGG_CUDA_OK(cudaStreamSynchronize(st));
+    }
     return 0;
 }
