@@ -60,8 +60,8 @@ static CUtensorMapL2promotion l2_promotion() {
     static int v = -1;
     if (v < 0) {
         const char* e = getenv("IGG_L2_PROMO");
-        v = e ? atoi(e) : 2;
-        if (v < 0 || v > 3) v = 2;
+        v = e ? atoi(e) : 1;
+        if (v < 0 || v > 3) v = 1;
     }
     return (CUtensorMapL2promotion)v;
 }

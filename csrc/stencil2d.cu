@@ -302,6 +302,239 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
 }
 
 // ------------------------------------------------------------------------------------------------
+// variant 1, whole-interior steps (mode 0): strip-marching kernel
+// ------------------------------------------------------------------------------------------------
+// A work item is a strip of BY columns marched down x for up to SNB blocks of SRB rows.  The producer
+// streams the T blocks (SRB x (BY+4), no row halo) through a 4-slot ring, the Cp blocks through a 2-slot
+// ring and the two halo rows of the chunk (above the first / below the last block) into a small
+// double-buffered slot; consumers compute block b from blocks b-1, b, b+1 and hand block b-1 back.  Every
+// row of T is fetched once per strip: the two halo rows per 32-row tile that the tile kernel re-fetches
+// (6 % of its T traffic) shrink to two per 256 rows.
+constexpr int SRB = 32;                     // rows per block
+constexpr int SNB = 8;                      // blocks per chunk
+constexpr int SCX = SRB * SNB;              // rows per work item (256)
+constexpr int SNT = 4, SNC = 2;             // ring depths
+constexpr int ST_BYTES = SRB * TP * 8;      // 33792 (multiple of 128)
+constexpr int SH_BYTES = TP * 8;            // 1056: one halo row
+constexpr int SH_PAD = 1152;
+constexpr int SSMEM_BYTES = SNT * ST_BYTES + SNC * CP_TILE_BYTES + 4 * SH_PAD + 256;
+
+template <int RPT>
+__global__ void __launch_bounds__((BY / 2) * (SRB / RPT) + 32, 1)
+diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapRow,
+                    const __grid_constant__ CUtensorMap mapCp, const __grid_constant__ Params p) {
+    constexpr int CONSUMERS = (BY / 2) * (SRB / RPT);
+    constexpr int NCW = CONSUMERS / 32;
+    constexpr int NRG = SRB / RPT;          // row groups per block
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char* ringT = smem;
+    unsigned char* ringC = smem + SNT * ST_BYTES;
+    unsigned char* halo = ringC + SNC * CP_TILE_BYTES;          // [parity][top, bottom]
+    uint64_t* fullT = reinterpret_cast<uint64_t*>(halo + 4 * SH_PAD);
+    uint64_t* emptyT = fullT + SNT;
+    uint64_t* fullC = emptyT + SNT;
+    uint64_t* emptyC = fullC + SNC;
+    uint64_t* fullH = emptyC + SNC;
+    uint64_t* emptyH = fullH + 2;
+    const int tid = threadIdx.x;
+    const int first = blockIdx.x;
+    const int n_my = first < p.ts.ntiles ? (p.ts.ntiles - first + gridDim.x - 1) / gridDim.x : 0;
+    if (tid == 0) {
+        for (int s = 0; s < SNT; ++s) { mbar_init(&fullT[s], 1); mbar_init(&emptyT[s], NCW); }
+        for (int s = 0; s < SNC; ++s) { mbar_init(&fullC[s], 1); mbar_init(&emptyC[s], NCW); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&fullH[s], 1); mbar_init(&emptyH[s], NCW); }
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (tid >= CONSUMERS) {
+        // ===== producer ===================================================================================
+        if (tid == CONSUMERS) {
+            tma_prefetch_desc(&mapT);
+            tma_prefetch_desc(&mapRow);
+            tma_prefetch_desc(&mapCp);
+            unsigned tq = 0, cq = 0;
+            auto issue_T = [&](int x, int j) {
+                const unsigned s = tq % SNT;
+                if (tq >= SNT) mbar_wait(&emptyT[s], ((tq / SNT) - 1) & 1);
+                mbar_arrive_expect_tx(&fullT[s], ST_BYTES);
+                tma_load_2d(ringT + s * ST_BYTES, &mapT, &fullT[s], j * BY - 2, x);
+                ++tq;
+            };
+            auto issue_C = [&](int x, int j) {
+                const unsigned s = cq % SNC;
+                if (cq >= SNC) mbar_wait(&emptyC[s], ((cq / SNC) - 1) & 1);
+                mbar_arrive_expect_tx(&fullC[s], CP_TILE_BYTES);
+                tma_load_2d(ringC + s * CP_TILE_BYTES, &mapCp, &fullC[s], j * BY, x);
+                ++cq;
+            };
+            for (int it = 0; it < n_my; ++it) {
+                int ci, j;
+                tile_of(p.ts, first + it * gridDim.x, ci, j);
+                if (p.has_push && wait_faces_2d(p.push, ci == 0, ci == p.i_hi, j == 0, j == p.j_hi))
+                    fence_proxy_async();
+                const int x0 = ci * SCX;
+                const int nb = (min(SCX, p.nx - x0) + SRB - 1) / SRB;
+                const int hp = it & 1;
+                if (it >= 2) mbar_wait(&emptyH[hp], ((it / 2) - 1) & 1);
+                mbar_arrive_expect_tx(&fullH[hp], 2 * SH_BYTES);
+                tma_load_2d(halo + (2 * hp) * SH_PAD, &mapRow, &fullH[hp], j * BY - 2, x0 - 1);
+                tma_load_2d(halo + (2 * hp + 1) * SH_PAD, &mapRow, &fullH[hp], j * BY - 2, x0 + nb * SRB);
+                issue_T(x0, j);
+                for (int b = 0; b < nb; ++b) {
+                    if (b + 1 < nb) issue_T(x0 + (b + 1) * SRB, j);
+                    issue_C(x0 + b * SRB, j);
+                }
+            }
+        }
+        return;
+    }
+
+    // ===== consumers ====================================================================================
+    const int cp = tid % (BY / 2);   // column pair
+    const int rg = tid / (BY / 2);   // row group inside a block
+    const double lam = p.dev_params ? p.dev_params[0] : p.lam, dt = p.dev_params ? p.dev_params[1] : p.dt;
+    const double _dx = p.dev_params ? p.dev_params[2] : p._dx, _dy = p.dev_params ? p.dev_params[3] : p._dy;
+    const bool diag = p.diag_out != nullptr;
+    double dmax = -INFINITY, dsum = 0.0;
+    unsigned tq = 0, cq = 0;
+    const int col = 2 * cp + 2;      // smem column of the thread's first cell
+
+    for (int it = 0; it < n_my; ++it) {
+        int ci, j;
+        tile_of(p.ts, first + it * gridDim.x, ci, j);
+        const int x0 = ci * SCX;
+        const int nb = (min(SCX, p.nx - x0) + SRB - 1) / SRB;
+        const int hp = it & 1;
+        const bool e_xl = ci == 0 && p.side_nb[0], e_xh = ci == p.i_hi && p.side_nb[1];
+        const bool e_yl = j == 0 && p.side_nb[2], e_yh = j == p.j_hi && p.side_nb[3];
+        const bool edge_tile = p.has_push && (e_xl || e_xh || e_yl || e_yh);
+        const int y = j * BY + 2 * cp;
+        const bool vy0 = (y >= 1) && (y <= p.ny - 2);
+        const bool vy1 = (y + 1 <= p.ny - 2);
+        mbar_wait(&fullH[hp], (it / 2) & 1);
+        mbar_wait(&fullT[tq % SNT], (tq / SNT) & 1);
+        const double* hTop = reinterpret_cast<const double*>(halo + (2 * hp) * SH_PAD);
+        const double* hBot = reinterpret_cast<const double*>(halo + (2 * hp + 1) * SH_PAD);
+        for (int b = 0; b < nb; ++b) {
+            const unsigned qb = tq + b, qc = cq + b;
+            if (b + 1 < nb) mbar_wait(&fullT[(qb + 1) % SNT], ((qb + 1) / SNT) & 1);
+            mbar_wait(&fullC[qc % SNC], (qc / SNC) & 1);
+            const double* cur = reinterpret_cast<const double*>(ringT + (qb % SNT) * ST_BYTES);
+            // row above the block's first row / below its last row live in the neighbouring ring slots
+            // (or in the chunk's halo rows)
+            const double* above = b > 0 ? reinterpret_cast<const double*>(ringT + ((qb - 1) % SNT) * ST_BYTES) +
+                                              (SRB - 1) * TP
+                                        : hTop;
+            const double* below = b + 1 < nb ? reinterpret_cast<const double*>(ringT + ((qb + 1) % SNT) * ST_BYTES)
+                                             : hBot;
+            const double* sC = reinterpret_cast<const double*>(ringC + (qc % SNC) * CP_TILE_BYTES) +
+                               (rg * RPT) * BY + 2 * cp;
+            const int lr0 = rg * RPT;
+            const double* r_m1 = lr0 > 0 ? cur + (lr0 - 1) * TP : above;
+            double2 a = *reinterpret_cast<const double2*>(r_m1 + col);
+            double2 bb = *reinterpret_cast<const double2*>(cur + lr0 * TP + col);
+            const int xb = x0 + b * SRB + lr0;
+#pragma unroll
+            for (int r = 0; r < RPT; ++r) {
+                const double* rc = cur + (lr0 + r) * TP;                                   // this row
+                const double* rn = (lr0 + r + 1 < SRB) ? rc + TP : below;                  // next row
+                const double2 c = *reinterpret_cast<const double2*>(rn + col);
+                const double bl = rc[col - 1];
+                const double br = rc[col + 2];
+                const double2 cc = *reinterpret_cast<const double2*>(sC + r * BY);
+                const int x = xb + r;
+                const double vA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, lam, dt, _dx, _dy);
+                const double vB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, lam, dt, _dx, _dy);
+                const bool vx = (x >= 1) && (x <= p.nx - 2);
+                const bool wA = vx && vy0, wB = vx && vy1;
+                double* out = p.T2 + (size_t)x * p.ny + y;
+                if (wA && wB) {
+                    st_cs_f64x2(out, vA, vB);
+                } else {
+                    if (wA) st_cs_f64(out, vA);
+                    if (wB) st_cs_f64(out + 1, vB);
+                }
+                if (edge_tile) {
+                    if (wA) push_cell_2d(p.push, p.nx, p.ny, x, y, vA);
+                    if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
+                }
+                if (diag) {
+                    if (wA) { dmax = fmax(dmax, vA); dsum += vA; }
+                    if (wB) { dmax = fmax(dmax, vB); dsum += vB; }
+                }
+                a = bb;
+                bb = c;
+            }
+            // block b-1 and this Cp block are no longer needed
+            __syncwarp();
+            if ((tid & 31) == 0) {
+                if (b > 0) mbar_arrive(&emptyT[(qb - 1) % SNT]);
+                mbar_arrive(&emptyC[qc % SNC]);
+            }
+        }
+        __syncwarp();
+        if ((tid & 31) == 0) {
+            mbar_arrive(&emptyT[(tq + nb - 1) % SNT]);
+            mbar_arrive(&emptyH[hp]);
+        }
+        tq += nb;
+        cq += nb;
+        if (edge_tile) {
+            consumer_sync(CONSUMERS);
+            if (tid == 0) signal_edges_2d(p.push, p.edge_tiles, e_xl, e_xh, e_yl, e_yh);
+        }
+    }
+
+    if (diag) {
+        __shared__ double red[64];
+        __shared__ bool is_last;
+        auto block_fold = [&](double& mx, double& sm) {
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                sm += __shfl_xor_sync(0xffffffffu, sm, off);
+            }
+            if ((tid & 31) == 0) { red[tid >> 5] = mx; red[32 + (tid >> 5)] = sm; }
+            consumer_sync(CONSUMERS);
+            if (tid < 32) {
+                mx = tid < NCW ? red[tid] : -INFINITY;
+                sm = tid < NCW ? red[32 + tid] : 0.0;
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) {
+                    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                    sm += __shfl_xor_sync(0xffffffffu, sm, off);
+                }
+            }
+            consumer_sync(CONSUMERS);
+        };
+        block_fold(dmax, dsum);
+        if (tid == 0) {
+            p.diag->pmax[blockIdx.x] = dmax;
+            p.diag->psum[blockIdx.x] = dsum;
+            __threadfence();
+            is_last = atomicAdd(&p.diag->ticket, 1u) == gridDim.x - 1;
+        }
+        consumer_sync(CONSUMERS);
+        if (is_last) {
+            __threadfence();
+            dmax = -INFINITY;
+            dsum = 0.0;
+            for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS) {
+                dmax = fmax(dmax, p.diag->pmax[b2]);
+                dsum += p.diag->psum[b2];
+            }
+            block_fold(dmax, dsum);
+            if (tid == 0) {
+                p.diag_out[0] = dmax;
+                p.diag_out[1] = dsum;
+                p.diag->ticket = 0;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // variant 0: direct global loads, one CTA per tile, one cell per thread per row
 // ------------------------------------------------------------------------------------------------
 constexpr int DBX = 16;
@@ -437,6 +670,29 @@ static int launch_tma(const CUtensorMap& mT, const CUtensorMap& mC, const Params
     return 0;
 }
 
+static int launch_strip(const CUtensorMap& mT, const CUtensorMap& mRow, const CUtensorMap& mC, const Params& p,
+                        cudaStream_t st) {
+    auto kern = diff2d_strip_kernel<4>;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    IGG_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SSMEM_BYTES));
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    const int sms = igg::sm_count();
+    const int grid = p.ts.ntiles < sms ? p.ts.ntiles : sms;
+    kern<<<grid, (BY / 2) * (SRB / 4) + 32, SSMEM_BYTES, st>>>(mT, mRow, mC, p);
+    return 0;
+}
+
+// which TMA kernel serves whole-interior steps: 1 = strip marching (default), 0 = tiles
+static int use_strip_kernel() {
+    static int v = -1;
+    if (v < 0) v = env_int("IGG_TMA_STRIP", 1);
+    return v;
+}
+
 }  // namespace
 
 extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
@@ -459,9 +715,12 @@ extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* C
     IGG_REQUIRE(!p.diag_out || (p.diag && variant == 1),
                 "igg_diffusion2d_step: diag_out needs diag_scratch and the TMA variant (variant 1)");
     p.mode = mode; p.bwx = bwx; p.bwy = bwy;
-    p.i_hi = (nx - 2) / BX;
+    // whole-interior steps of large grids go to the strip-marching kernel (work items of SCX x BY cells)
+    const bool strip = variant == 1 && mode == 0 && use_strip_kernel() && nx >= 2 * SCX;
+    const int tile_x = strip ? SCX : BX;
+    p.i_hi = (nx - 2) / tile_x;
     p.j_hi = (ny - 2) / BY;
-    build_tiles(p.ts, nx, ny, mode, bwx, bwy);
+    build_tiles(p.ts, nx, ny, mode, bwx, bwy, tile_x, BY);
     if (p.ts.ntiles == 0) return 0;
     p.has_push = push ? 1 : 0;
     const int nti = p.i_hi + 1, ntj = p.j_hi + 1;
@@ -498,10 +757,21 @@ extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* C
         if (rc) return rc;
         rc = igg::get_tensor_map_f64(Cp, 2, dims, boxC, &mC);
         if (rc) return rc;
-        switch (tma_rows_per_thread()) {
-            case 4: rc = launch_tma<4>(mT, mC, p, st); break;    // 16 consumer warps
-            case 16: rc = launch_tma<16>(mT, mC, p, st); break;  // 4 consumer warps
-            default: rc = launch_tma<8>(mT, mC, p, st); break;   // 8 consumer warps
+        if (strip) {
+            CUtensorMap mB, mRow;
+            const uint32_t boxB[2] = {TP, SRB};
+            const uint32_t boxR[2] = {TP, 1};
+            rc = igg::get_tensor_map_f64(T, 2, dims, boxB, &mB);
+            if (rc) return rc;
+            rc = igg::get_tensor_map_f64(T, 2, dims, boxR, &mRow);
+            if (rc) return rc;
+            rc = launch_strip(mB, mRow, mC, p, st);
+        } else {
+            switch (tma_rows_per_thread()) {
+                case 4: rc = launch_tma<4>(mT, mC, p, st); break;    // 16 consumer warps
+                case 16: rc = launch_tma<16>(mT, mC, p, st); break;  // 4 consumer warps
+                default: rc = launch_tma<8>(mT, mC, p, st); break;   // 8 consumer warps
+            }
         }
         if (rc) return rc;
         IGG_LAUNCH_CHECK();

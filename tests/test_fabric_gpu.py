@@ -64,6 +64,28 @@ def test_solver_periodic_self_neighbor(variant, mode):
     assert float((s.T.cpu() - T).abs().max()) < 1e-13
 
 
+def test_strip_kernel_periodic_self_neighbor():
+    """Large enough for the strip-marching kernel: its in-kernel push / flags against itself."""
+    from rocm_mpi_b200.models.solver import Diffusion2D
+    nx, ny = 600, 260
+    igg.init_global_grid(nx, ny, 1, periodx=1, periody=1, quiet=True, init_dist=False)
+    s = Diffusion2D(nx, ny, mode="fused", variant="tma")
+    T = s.T.cpu().clone()
+    s.begin()
+    s.step(1)
+    s.step(4)
+    s.finish()
+    vg = igg.VirtualGrid((nx, ny), (1, 1), (1, 1))
+    T2 = T.clone()
+    Cp = torch.ones_like(T)
+    vg.update_halo([T])
+    for _ in range(5):
+        ref.perf_step(T2, T, Cp, s.lam, s.dt, s._dx, s._dy)
+        vg.update_halo([T2])
+        T, T2 = T2, T
+    assert float((s.T.cpu() - T).abs().max()) < 1e-13
+
+
 def test_push_plan_3d_periodic_self():
     shape = (20, 18, 66)
     igg.init_global_grid(*shape, periodx=1, periody=1, periodz=1, quiet=True, init_dist=False)

@@ -204,3 +204,21 @@ def test_in_kernel_diagnostic_matches_torch():
             assert abs(float(got[1]) - float(inner.sum())) <= 1e-10 * abs(float(inner.sum())) + 1e-9
     with pytest.raises(native.NativeError):
         native.diffusion2d_step(T2d, T.cuda(), Cp.cuda(), 1.0, 1e-3, 2.0, 3.0, variant="direct", diag_out=out)
+
+
+@pytest.mark.parametrize("shape", [(512, 130), (520, 260), (777, 130), (1030, 1026), (2048, 384)])
+def test_strip_marching_kernel_matches_reference(shape):
+    """nx >= 512 selects the strip-marching TMA kernel for whole-interior steps (partial chunks / blocks / strips)."""
+    nx, ny = shape
+    T, Cp = _fields(nx, ny, 31)
+    want = T.clone()
+    ref.perf_step(want, T, Cp, 1.3, 1e-3, 2.0, 3.0)
+    T2d = T.cuda().clone()
+    out = torch.zeros(2, dtype=torch.float64, device="cuda")
+    native.diffusion2d_step(T2d, T.cuda(), Cp.cuda(), 1.3, 1e-3, 2.0, 3.0, variant="tma", diag_out=out)
+    got = T2d.cpu()
+    assert float((got - want).abs().max()) < TOL
+    assert torch.equal(got[0], T[0]) and torch.equal(got[-1], T[-1]) and torch.equal(got[:, 0], T[:, 0])
+    inner = want[1:-1, 1:-1]
+    assert abs(float(out[0]) - float(inner.max())) < 1e-14
+    assert abs(float(out[1]) - float(inner.sum())) <= 1e-10 * abs(float(inner.sum())) + 1e-9

@@ -15,7 +15,7 @@ def _ngpu():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
 
-@pytest.mark.parametrize("nprocs,args", [(2, (66, 260, 0, 0, 12)), (2, (66, 260, 1, 1, 8)), (4, (40, 132, 0, 1, 6)),
+@pytest.mark.parametrize("nprocs,args", [(2, (66, 260, 0, 0, 12)), (2, (530, 260, 0, 1, 6)), (2, (66, 260, 1, 1, 8)), (4, (40, 132, 0, 1, 6)),
                                          (8, (34, 130, 0, 0, 6))])
 def test_peer_fabric_and_solver_multi_gpu(nprocs, args):
     if _ngpu() < nprocs:
