@@ -76,6 +76,7 @@ struct Params {
     int has_push;
     int edge_tiles[9];
     int side_nb[4];             // does ANY neighbour exist on the x-low / x-high / y-low / y-high side
+    int scx;                    // strip kernel: rows per work item (multiple of its block height)
     igg_push2d push;
 };
 
@@ -304,15 +305,14 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
 // ------------------------------------------------------------------------------------------------
 // variant 1, whole-interior steps (mode 0): strip-marching kernel
 // ------------------------------------------------------------------------------------------------
-// A work item is a strip of BY columns marched down x for up to SNB blocks of SRB rows.  The producer
+// A work item is a strip of BY columns marched down x for p.scx rows in blocks of SRB rows.  The producer
 // streams the T blocks (SRB x (BY+4), no row halo) through a 4-slot ring, the Cp blocks through a 2-slot
 // ring and the two halo rows of the chunk (above the first / below the last block) into a small
 // double-buffered slot; consumers compute block b from blocks b-1, b, b+1 and hand block b-1 back.  Every
 // row of T is fetched once per strip: the two halo rows per 32-row tile that the tile kernel re-fetches
 // (6 % of its T traffic) shrink to two per 256 rows.
 constexpr int SRB = 32;                     // rows per block
-constexpr int SNB = 8;                      // blocks per chunk
-constexpr int SCX = SRB * SNB;              // rows per work item (256)
+constexpr int SCX_DEFAULT = 8 * SRB;        // rows per work item (256); IGG_STRIP_ROWS overrides
 constexpr int SNT = 4, SNC = 2;             // ring depths
 constexpr int ST_BYTES = SRB * TP * 8;      // 33792 (multiple of 128)
 constexpr int SH_BYTES = TP * 8;            // 1056: one halo row
@@ -373,8 +373,8 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
                 tile_of(p.ts, first + it * gridDim.x, ci, j);
                 if (p.has_push && wait_faces_2d(p.push, ci == 0, ci == p.i_hi, j == 0, j == p.j_hi))
                     fence_proxy_async();
-                const int x0 = ci * SCX;
-                const int nb = (min(SCX, p.nx - x0) + SRB - 1) / SRB;
+                const int x0 = ci * p.scx;
+                const int nb = (min(p.scx, p.nx - x0) + SRB - 1) / SRB;
                 const int hp = it & 1;
                 if (it >= 2) mbar_wait(&emptyH[hp], ((it / 2) - 1) & 1);
                 mbar_arrive_expect_tx(&fullH[hp], 2 * SH_BYTES);
@@ -403,8 +403,8 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
     for (int it = 0; it < n_my; ++it) {
         int ci, j;
         tile_of(p.ts, first + it * gridDim.x, ci, j);
-        const int x0 = ci * SCX;
-        const int nb = (min(SCX, p.nx - x0) + SRB - 1) / SRB;
+        const int x0 = ci * p.scx;
+        const int nb = (min(p.scx, p.nx - x0) + SRB - 1) / SRB;
         const int hp = it & 1;
         const bool e_xl = ci == 0 && p.side_nb[0], e_xh = ci == p.i_hi && p.side_nb[1];
         const bool e_yl = j == 0 && p.side_nb[2], e_yh = j == p.j_hi && p.side_nb[3];
@@ -447,7 +447,12 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
                 const double vA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, lam, dt, _dx, _dy);
                 const double vB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, lam, dt, _dx, _dy);
                 const bool vx = (x >= 1) && (x <= p.nx - 2);
-                const bool wA = vx && vy0, wB = vx && vy1;
+                bool wA = vx && vy0, wB = vx && vy1;
+                if (p.mode != 0) {
+                    const bool fA = in_frame(p, x, y), fB = in_frame(p, x, y + 1);
+                    wA = wA && (p.mode == 1 ? fA : !fA);
+                    wB = wB && (p.mode == 1 ? fB : !fB);
+                }
                 double* out = p.T2 + (size_t)x * p.ny + y;
                 if (wA && wB) {
                     st_cs_f64x2(out, vA, vB);
@@ -715,9 +720,16 @@ extern "C" int igg_diffusion2d_step(const double* T, double* T2, const double* C
     IGG_REQUIRE(!p.diag_out || (p.diag && variant == 1),
                 "igg_diffusion2d_step: diag_out needs diag_scratch and the TMA variant (variant 1)");
     p.mode = mode; p.bwx = bwx; p.bwy = bwy;
-    // whole-interior steps of large grids go to the strip-marching kernel (work items of SCX x BY cells)
-    const bool strip = variant == 1 && mode == 0 && use_strip_kernel() && nx >= 2 * SCX;
-    const int tile_x = strip ? SCX : BX;
+    // whole-interior (mode 0) and inside-the-frame (mode 2) steps of large grids go to the strip-marching
+    // kernel (work items of scx x BY cells); the thin boundary frame (mode 1) stays with the tile kernel
+    static int scx_env = -1;
+    if (scx_env < 0) {
+        scx_env = env_int("IGG_STRIP_ROWS", SCX_DEFAULT);
+        if (scx_env < SRB || scx_env % SRB) scx_env = SCX_DEFAULT;
+    }
+    p.scx = scx_env;
+    const bool strip = variant == 1 && (mode == 0 || mode == 2) && use_strip_kernel() && nx >= 2 * SCX_DEFAULT;
+    const int tile_x = strip ? p.scx : BX;
     p.i_hi = (nx - 2) / tile_x;
     p.j_hi = (ny - 2) / BY;
     build_tiles(p.ts, nx, ny, mode, bwx, bwy, tile_x, BY);

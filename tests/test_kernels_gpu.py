@@ -53,7 +53,7 @@ def test_direct_variant_handles_odd_ny_and_tma_rejects_it():
 
 @pytest.mark.parametrize("variant", ["direct", "tma"])
 @pytest.mark.parametrize("shape,bw", [((200, 520), (16, 4)), ((70, 300), (32, 8)), ((40, 40), (30, 30)),
-                                      ((300, 260), (1, 1))])
+                                      ((300, 260), (1, 1)), ((600, 300), (16, 4)), ((1100, 260), (40, 130))])
 def test_split_step_frame_then_interior(variant, shape, bw):
     nx, ny = shape
     T, Cp = _fields(nx, ny, 3)
