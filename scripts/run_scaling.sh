@@ -24,4 +24,4 @@ except Exception as ex:
 PY
 }
 for n in 1 2 4 8; do [ $n -le $MAXN ] && run $n ours; done
-for impl in nccl nccl_tma plain_peer hide; do run $MAXN $impl --no-e2e; done
+for impl in ${ARMS:-nccl nccl_tma plain_peer hide}; do run $MAXN $impl --no-e2e; done
