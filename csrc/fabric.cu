@@ -51,7 +51,12 @@ __global__ void __launch_bounds__(HX_THREADS) halo_exchange_kernel(const igg_hal
             const size_t c = e % e2, b = (e / e2) % e1, a = e / (e1 * e2);
             const size_t si = ((a + t.src_start[0]) * t.n[1] + (b + t.src_start[1])) * t.n[2] + (c + t.src_start[2]);
             const size_t di = ((a + t.dst_start[0]) * t.n[1] + (b + t.dst_start[1])) * t.n[2] + (c + t.dst_start[2]);
-            t.dst[di] = t.src[si];
+            switch (t.elem_bytes) {
+                case 8: ((uint64_t*)t.dst)[di] = ((const uint64_t*)t.src)[si]; break;
+                case 4: ((uint32_t*)t.dst)[di] = ((const uint32_t*)t.src)[si]; break;
+                case 2: ((uint16_t*)t.dst)[di] = ((const uint16_t*)t.src)[si]; break;
+                default: ((uint8_t*)t.dst)[di] = ((const uint8_t*)t.src)[si]; break;
+            }
         }
     }
     // (3) last CTA to finish releases the epoch to every neighbour

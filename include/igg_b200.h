@@ -182,12 +182,14 @@ int igg_can_access_peer(int dev, int peer_dev, int* can);
  * all boxes stored into the neighbours' arrays -> release the epoch -> wait for the neighbours'.
  * `xfers` lives in device memory. */
 typedef struct igg_halo_xfer {
-    const double* src;              /* my array                                                   */
-    double* dst;                    /* the neighbour's array (peer-mapped; same shape)            */
+    const void* src;                /* my array                                                   */
+    void* dst;                      /* the neighbour's array (peer-mapped; same shape)            */
     int n[3];                       /* array shape (1 for unused trailing dims)                   */
     int src_start[3];
     int dst_start[3];
     int extent[3];
+    int elem_bytes;                 /* 8, 4, 2 or 1 (any field dtype of that size)                */
+    int reserved;
 } igg_halo_xfer;
 typedef struct igg_halo_sync {
     uint64_t* peer_bank[27];        /* flag bank base in the pad of the neighbour at offset o (NULL = none) */

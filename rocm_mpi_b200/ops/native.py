@@ -22,9 +22,6 @@ FLAG_BANKS, BANK_STRIDE = 32, 64
 SLOT_DATA, SLOT_READY, SLOT_ERR, SLOT_CTA_COUNT = 0, 27, 54, 55
 MAX_HALO_FIELDS = 8
 
-c_f64p = C.c_void_p
-c_u64p = C.c_void_p
-
 
 class Push2D(C.Structure):
     _fields_ = [("peer_dst", C.c_void_p * 9), ("peer_flag", C.c_void_p * 9), ("my_flag", C.c_void_p * 9),
@@ -42,7 +39,7 @@ class StepOpts(C.Structure):
 
 class HaloXfer(C.Structure):
     _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("n", C.c_int * 3), ("src_start", C.c_int * 3),
-                ("dst_start", C.c_int * 3), ("extent", C.c_int * 3)]
+                ("dst_start", C.c_int * 3), ("extent", C.c_int * 3), ("elem_bytes", C.c_int), ("reserved", C.c_int)]
 
 
 class HaloSync(C.Structure):

@@ -261,13 +261,13 @@ class PeerHalo:
             yield o, ranks[o], src, dst, ext
 
     def _table(self, fields: Sequence[torch.Tensor]):
-        key = tuple((A.data_ptr(), tuple(A.shape)) for A in fields)
+        key = tuple((A.data_ptr(), tuple(A.shape), A.element_size()) for A in fields)
         hit = self._tables.get(key)
         if hit is not None:
             return hit
         for A in fields:
-            if A.dtype != torch.float64:
-                raise TypeError("the peer transport moves float64 fields")
+            if A.element_size() not in (1, 2, 4, 8):
+                raise TypeError(f"the peer transport moves 1/2/4/8-byte elements, not {A.dtype}")
             self.fab.register(A)          # collective on first sight of a field
         xf: List[native.HaloXfer] = []
         for A in fields:
@@ -281,6 +281,7 @@ class PeerHalo:
                     x.src_start[d] = src[d]
                     x.dst_start[d] = dst[d]
                     x.extent[d] = ext[d]
+                x.elem_bytes = A.element_size()
                 xf.append(x)
         n = len(xf)
         if n:

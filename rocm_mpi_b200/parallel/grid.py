@@ -202,17 +202,26 @@ def finalize_global_grid(*, finalize_dist: bool = True) -> None:
     _GRID = None
 
 
-def nx_g() -> int:
-    """Global number of grid points in x (reference ``scripts/diffusion_2D_ap.jl:19``)."""
-    return global_grid().nxyz_g[0]
+def _n_g(dim: int, A=None) -> int:
+    g = global_grid()
+    if A is None:
+        return g.nxyz_g[dim]
+    size = A.shape[dim] if dim < A.dim() else 1
+    return g.nxyz_g[dim] + (size - g.nxyz[dim])       # staggered arrays: same shift as locally
 
 
-def ny_g() -> int:
-    return global_grid().nxyz_g[1]
+def nx_g(A=None) -> int:
+    """Global number of grid points in x (reference ``scripts/diffusion_2D_ap.jl:19``); with a field
+    argument, the global size of that (possibly staggered) field, as upstream ``nx_g(A)``."""
+    return _n_g(0, A)
 
 
-def nz_g() -> int:
-    return global_grid().nxyz_g[2]
+def ny_g(A=None) -> int:
+    return _n_g(1, A)
+
+
+def nz_g(A=None) -> int:
+    return _n_g(2, A)
 
 
 def ol(dim: int, A=None) -> int:

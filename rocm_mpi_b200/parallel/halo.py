@@ -159,7 +159,7 @@ class ExchangeHalo:
 
     # -- pack / unpack -----------------------------------------------------------------
     def _pack(self, A: torch.Tensor, dim: int, idx: int, out: torch.Tensor) -> None:
-        if A.is_cuda:
+        if A.is_cuda and A.dtype == torch.float64:
             from ..ops import native
             if native.available():
                 native.pack_plane(A, dim, idx, out)
@@ -168,7 +168,7 @@ class ExchangeHalo:
         out.view(A.select(dim, idx).shape).copy_(A.select(dim, idx))
 
     def _unpack(self, A: torch.Tensor, dim: int, idx: int, src: torch.Tensor) -> None:
-        if A.is_cuda:
+        if A.is_cuda and A.dtype == torch.float64:
             from ..ops import native
             if native.available():
                 native.unpack_plane(A, dim, idx, src)

@@ -64,6 +64,18 @@ def test_solver_periodic_self_neighbor(variant, mode):
     assert float((s.T.cpu() - T).abs().max()) < 1e-13
 
 
+def test_update_halo_peer_other_dtypes():
+    igg.init_global_grid(12, 10, 1, periodx=1, periody=1, quiet=True, init_dist=False)
+    vg = igg.VirtualGrid((12, 10), (1, 1), (1, 1))
+    g = torch.Generator().manual_seed(9)
+    for dt in (torch.float32, torch.int64, torch.int16, torch.uint8):
+        A = (torch.rand(12, 10, generator=g) * 100).to(dt)
+        Ad = A.cuda()
+        igg.update_halo(Ad, transport="peer")
+        vg.update_halo([A])
+        assert torch.equal(Ad.cpu(), A), dt
+
+
 def test_strip_kernel_periodic_self_neighbor():
     """Large enough for the strip-marching kernel: its in-kernel push / flags against itself."""
     from rocm_mpi_b200.models.solver import Diffusion2D

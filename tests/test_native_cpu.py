@@ -15,7 +15,7 @@ def test_library_loads_and_reports_version():
 def test_struct_layouts_match_header():
     assert ctypes.sizeof(native.Push2D) == 9 * 8 * 4 + 16
     assert ctypes.sizeof(native.Push3D) == 27 * 8 * 4 + 16
-    assert ctypes.sizeof(native.HaloXfer) == 16 + 4 * 12
+    assert ctypes.sizeof(native.HaloXfer) == 16 + 4 * 12 + 8
     assert ctypes.sizeof(native.HaloSync) == 27 * 8 + 24
 
 

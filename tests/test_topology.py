@@ -77,6 +77,7 @@ def test_global_coordinates():
     xs = igg.coords_g(0, dx, T)
     assert torch.equal(xs, torch.arange(8, dtype=torch.float64) * dx)
     assert igg.ol(0, T) == 2 and igg.ol(0, qx) == 1 and igg.ol(0, Vx) == 3
+    assert igg.nx_g(T) == 8 and igg.nx_g(qx) == 7 and igg.nx_g(Vx) == 9 and igg.ny_g(qx) == 6
 
 
 def test_global_coordinates_periodic():
