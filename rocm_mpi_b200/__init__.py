@@ -12,3 +12,18 @@ from .parallel import (PROC_NULL, VirtualGrid, a_eff, coords_g, dims_create, fin
                        nx_g, ny_g, nz_g, ol, select_device, t_eff, tic, toc, update_halo, x_g, y_g, z_g)
 
 __version__ = "0.1.0"
+
+
+def zeros(shape, dtype=None, symmetric: bool = True):
+    """Zero-filled field on this rank's device.
+
+    On CUDA with ``symmetric=True`` (default) the field lives in peer-addressable fabric memory (a
+    collective call), which is what the fused kernels and the ``peer`` transport of ``update_halo`` use
+    without a registration step; otherwise it is an ordinary ``torch.zeros`` tensor."""
+    import torch
+    from .parallel.fabric import fabric_zeros
+    g = global_grid()
+    dtype = dtype or torch.float64
+    if g.device_type == "cuda" and symmetric:
+        return fabric_zeros(shape, dtype)
+    return torch.zeros(tuple(shape), dtype=dtype, device=g.device)

@@ -46,7 +46,8 @@ class _DeviceBlock:
                                          "version": 3, "strides": None}
 
 
-_TYPESTR = {torch.float64: "<f8", torch.float32: "<f4", torch.int64: "<i8", torch.uint8: "|u1"}
+_TYPESTR = {torch.float64: "<f8", torch.float32: "<f4", torch.float16: "<f2", torch.int64: "<i8",
+            torch.int32: "<i4", torch.int16: "<i2", torch.uint8: "|u1"}
 
 
 def neighbor_offsets(g: GlobalGrid) -> List[Tuple[Tuple[int, int, int], int]]:

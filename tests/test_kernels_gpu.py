@@ -222,3 +222,16 @@ def test_strip_marching_kernel_matches_reference(shape):
     inner = want[1:-1, 1:-1]
     assert abs(float(out[0]) - float(inner.max())) < 1e-14
     assert abs(float(out[1]) - float(inner.sum())) <= 1e-10 * abs(float(inner.sum())) + 1e-9
+
+
+def test_strip_kernel_agrees_with_direct_kernel_at_bench_like_size():
+    """GPU-vs-GPU: the strip-marching TMA kernel and the direct-load kernel at a multi-chunk, many-strip size."""
+    nx, ny = 4100, 8200
+    g = torch.Generator(device="cuda").manual_seed(5)
+    T = torch.rand(nx, ny, generator=g, dtype=torch.float64, device="cuda")
+    Cp = torch.rand(nx, ny, generator=g, dtype=torch.float64, device="cuda") + 0.5
+    A, B = T.clone(), T.clone()
+    native.diffusion2d_step(A, T, Cp, 1.0, 1e-3, 2.0, 3.0, variant="tma")
+    native.diffusion2d_step(B, T, Cp, 1.0, 1e-3, 2.0, 3.0, variant="direct")
+    assert float((A - B).abs().max()) < 1e-13
+    assert torch.equal(A[0], T[0]) and torch.equal(A[:, -1], T[:, -1])
