@@ -41,7 +41,32 @@ struct ResParams {
     uint64_t* peer_flags[9];    // base of the neighbour's flag region
     uint64_t* my_flags;         // base of my flag region: slot [o * 16 + cta], error word at [9 * 16]
     uint64_t epoch0;            // epoch of step 0
+    // low-latency mode: every pushed value travels WITH its epoch (two 8-byte words {32 data bits, 32-bit
+    // epoch tag}) into a landing buffer of the neighbour, so no fence / flag round trip is needed
+    uint64_t* peer_land[9];     // base of the neighbour's landing buffer (NULL = flag mode or no neighbour)
+    uint64_t* my_land;          // mine: [parity][source offset][index along the edge][2 words]
+    int land_len;               // entries per (parity, offset) region
 };
+
+// landing-buffer helpers ---------------------------------------------------------------------------------
+__device__ __forceinline__ void ll_store(uint64_t* slot, double v, uint32_t tag) {
+    const uint64_t bits = (uint64_t)__double_as_longlong(v);
+    const uint64_t w0 = (bits & 0xffffffffull) | ((uint64_t)tag << 32);
+    const uint64_t w1 = (bits >> 32) | ((uint64_t)tag << 32);
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(slot), "l"(w0), "l"(w1) : "memory");
+}
+// spins until both words carry `tag`; returns false on timeout
+__device__ __forceinline__ bool ll_load(const uint64_t* slot, uint32_t tag, double& v) {
+    uint64_t w0, w1;
+    unsigned spins = 0;
+    while (true) {
+        asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(slot) : "memory");
+        if ((uint32_t)(w0 >> 32) == tag && (uint32_t)(w1 >> 32) == tag) break;
+        if (++spins > (1u << 26)) return false;
+    }
+    v = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+    return true;
+}
 
 __device__ __forceinline__ double upd(double c, double xm, double xp, double ym, double yp, double cp, double lam,
                                       double dt, double _dx, double _dy) {
@@ -79,9 +104,14 @@ __global__ void __launch_bounds__(RES_THREADS, 1) diff2d_resident_kernel(const _
     const bool has_up = c > 0, has_dn = (c + 1 < C) && ((c + 1) * R < nx);
     const bool own_row1 = (1 >= r0 && 1 < r0 + nr), own_rowN = (nx - 2 >= r0 && nx - 2 < r0 + nr);
     const bool own_row0 = (c == 0), own_rowL = (nx - 1 >= r0 && nx - 1 < r0 + nr);
+    const bool ll = p.my_land != nullptr;                   // low-latency (value + epoch tag) exchange
     bool has_peers = false;
+    bool nbr[9];                                            // is there a neighbour at offset o
 #pragma unroll
-    for (int o = 0; o < 9; ++o) has_peers |= p.peer_flags[o] != nullptr;
+    for (int o = 0; o < 9; ++o) {
+        nbr[o] = ll ? p.peer_land[o] != nullptr : p.peer_flags[o] != nullptr;
+        has_peers |= nbr[o];
+    }
 
     for (int s = 0; s < p.nsteps; ++s) {
         const bool even = (s & 1) == 0;
@@ -116,19 +146,58 @@ __global__ void __launch_bounds__(RES_THREADS, 1) diff2d_resident_kernel(const _
 #pragma unroll
                         for (int sy = -1; sy <= 1; ++sy) {
                             if ((sy == -1 && !yl) || (sy == 1 && !yh) || (sx == 0 && sy == 0)) continue;
-                            double* d = peers[(sx + 1) * 3 + (sy + 1)];
-                            if (!d) continue;
-                            const int dx = sx == -1 ? nx - 1 : (sx == 1 ? 0 : x);
-                            const int dy = sy == -1 ? ny - 1 : (sy == 1 ? 0 : y);
-                            d[(size_t)dx * ny + dy] = v;
+                            const int k = (sx + 1) * 3 + (sy + 1);
+                            if (ll) {
+                                // value + tag into the neighbour's landing region for source offset 8-k;
+                                // index along the edge: y for x-edges, x for y-edges, 0 for corners
+                                uint64_t* land = p.peer_land[k];
+                                if (!land) continue;
+                                const int idx = sx != 0 ? (sy == 0 ? y : 0) : x;
+                                ll_store(land + (((size_t)(epoch & 1) * 9 + (8 - k)) * p.land_len + idx) * 2, v,
+                                         (uint32_t)epoch);
+                            } else {
+                                double* d = peers[k];
+                                if (!d) continue;
+                                const int dx = sx == -1 ? nx - 1 : (sx == 1 ? 0 : x);
+                                const int dy = sy == -1 ? ny - 1 : (sy == 1 ? 0 : y);
+                                d[(size_t)dx * ny + dy] = v;
+                            }
                         }
                     }
                 }
             }
         }
-        if (has_peers) __syncthreads();
+        if (ll && has_peers) {
+            // ---- low-latency import: every halo cell polls its own landing slot until the epoch tag matches ----
+            const uint64_t* land = p.my_land + (size_t)(epoch & 1) * 9 * p.land_len * 2;
+            const uint32_t tag = (uint32_t)epoch;
+            bool ok = true;
+            double v;
+            if (nbr[3] || nbr[5]) {                                        // columns 0 / ny-1 of my rows
+                for (int lr = tid; lr < nr; lr += RES_THREADS) {
+                    const int x = r0 + lr;
+                    if (x < 1 || x > nx - 2) continue;
+                    if (nbr[3]) { ok &= ll_load(land + ((size_t)3 * p.land_len + x) * 2, tag, v); dst[(size_t)lr * ny] = v; }
+                    if (nbr[5]) { ok &= ll_load(land + ((size_t)5 * p.land_len + x) * 2, tag, v); dst[(size_t)lr * ny + ny - 1] = v; }
+                }
+            }
+            for (int side = 0; side < 2; ++side) {                          // row 0 / row nx-1
+                const bool own = side == 0 ? own_row0 : own_rowL;
+                if (!own || nr == 0) continue;
+                const int x = side == 0 ? 0 : nx - 1, lr = x - r0, o0 = side == 0 ? 0 : 6;
+                if (nbr[o0 + 1])
+                    for (int y = 1 + tid; y <= ny - 2; y += RES_THREADS) {
+                        ok &= ll_load(land + ((size_t)(o0 + 1) * p.land_len + y) * 2, tag, v);
+                        dst[(size_t)lr * ny + y] = v;
+                    }
+                if (tid == 0 && nbr[o0]) { ok &= ll_load(land + ((size_t)o0 * p.land_len) * 2, tag, v); dst[(size_t)lr * ny] = v; }
+                if (tid == 1 && nbr[o0 + 2]) { ok &= ll_load(land + ((size_t)(o0 + 2) * p.land_len) * 2, tag, v); dst[(size_t)lr * ny + ny - 1] = v; }
+            }
+            if (!ok) atomicExch((unsigned long long*)err, (unsigned long long)epoch | (1ull << 63));
+        }
+        if (!ll && has_peers) __syncthreads();
         // ---- announce my pushes: one flag per (neighbour offset, CTA) -------------------------------------
-        if (tid < 9 && tid != 4 && p.peer_flags[tid]) {
+        if (!ll && tid < 9 && tid != 4 && p.peer_flags[tid]) {
             const int sx = tid / 3 - 1, sy = tid % 3 - 1;
             const bool mine = (sx == -1 ? own_row1 : (sx == 1 ? own_rowN : true)) && nr > 0;
             // y-direction pushes come from every CTA; x-direction / corner pushes only from the row owner
@@ -140,7 +209,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) diff2d_resident_kernel(const _
         // ---- import the halo cells the neighbours pushed into my global array ------------------------------
         // which neighbours write into cells that live in MY rows: (0,-1)/(0,+1) for every CTA; (-1,*) for
         // the owner of row 0; (+1,*) for the owner of row nx-1.
-        if (tid < 9 && tid != 4 && p.peer_flags[tid]) {
+        if (!ll && tid < 9 && tid != 4 && p.peer_flags[tid]) {
             const int sx = tid / 3 - 1;
             const bool mine = (sx == -1 ? own_row0 : (sx == 1 ? own_rowL : true)) && nr > 0;
             // the sender of offset (sx, sy) cells is CTA c for sx == 0, and the owner of ITS row nx-2 / row 1
@@ -155,7 +224,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) diff2d_resident_kernel(const _
                 wait_flag_ge(p.my_flags + tid * 16 + sender, epoch, err);
             }
         }
-        if (has_peers) {
+        if (!ll && has_peers) {
             __syncthreads();
             const bool nb_yl = p.peer_flags[1 * 3 + 0] != nullptr, nb_yh = p.peer_flags[1 * 3 + 2] != nullptr;
             // columns 0 and ny-1 of my rows (rows 1..nx-2 only; corners belong to the row imports below)
@@ -197,11 +266,14 @@ __global__ void __launch_bounds__(RES_THREADS, 1) diff2d_resident_kernel(const _
 extern "C" int igg_diffusion2d_resident(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
                                         double _dx, double _dy, int nsteps, double* const* peer_T,
                                         double* const* peer_T2, uint64_t* const* peer_flags, uint64_t* my_flags,
-                                        uint64_t epoch0, int* cluster_size_out, void* stream) {
+                                        uint64_t epoch0, uint64_t* const* peer_land, uint64_t* my_land, int land_len,
+                                        int* cluster_size_out, void* stream) {
     IGG_REQUIRE(T && T2 && Cp && nx >= 3 && ny >= 3 && nsteps >= 1, "igg_diffusion2d_resident: bad arguments");
-    const bool comm = peer_flags != nullptr;
-    IGG_REQUIRE(!comm || (peer_T && peer_T2 && my_flags && epoch0 >= 1),
-                "igg_diffusion2d_resident: communication needs peer tables, flags and epoch0 >= 1");
+    const bool comm = peer_flags != nullptr || peer_land != nullptr;
+    IGG_REQUIRE(!comm || (my_flags && epoch0 >= 1), "igg_diffusion2d_resident: communication needs my_flags and epoch0 >= 1");
+    IGG_REQUIRE(!peer_flags || (peer_T && peer_T2), "igg_diffusion2d_resident: flag mode needs the peer array tables");
+    IGG_REQUIRE(!peer_land || (my_land && land_len >= (nx > ny ? nx : ny)),
+                "igg_diffusion2d_resident: landing buffers need land_len >= max(nx, ny)");
     int dev = 0, smem_max = 0;
     IGG_CUDA_OK(cudaGetDevice(&dev));
     IGG_CUDA_OK(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
@@ -227,12 +299,19 @@ extern "C" int igg_diffusion2d_resident(double* T, double* T2, const double* Cp,
     p.lam = lam; p.dt = dt; p._dx = _dx; p._dy = _dy;
     if (comm) {
         for (int o = 0; o < 9; ++o) {
-            p.peer_T[o] = peer_T[o];
-            p.peer_T2[o] = peer_T2[o];
-            p.peer_flags[o] = peer_flags[o];
+            if (peer_flags && !peer_land) {
+                p.peer_T[o] = peer_T[o];
+                p.peer_T2[o] = peer_T2[o];
+                p.peer_flags[o] = peer_flags[o];
+            }
+            if (peer_land) p.peer_land[o] = peer_land[o];
         }
         p.my_flags = my_flags;
         p.epoch0 = epoch0;
+        if (peer_land) {
+            p.my_land = my_land;
+            p.land_len = land_len;
+        }
     }
     static bool attr_set[64] = {false};
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {

@@ -112,10 +112,17 @@ int igg_diffusion2d_multistep(double* T, double* T2, const double* Cp, int nx, i
  * Result in T2 if nsteps is odd, else in T.  Tables are indexed [(ox+1)*3 + (oy+1)]; `peer_flags[o]` is the
  * base of the flag region (>= 9*16+1 uint64, zero-initialised, fabric memory) of the neighbour at offset o,
  * `my_flags` mine; `epoch0` is the epoch of step 0 and must grow by nsteps from call to call.  Pass
- * peer_flags == NULL for a run without communication. */
+ * peer_flags == NULL (and peer_land == NULL) for a run without communication.
+ * Low-latency mode (`peer_land` != NULL, takes precedence): instead of storing into the neighbours' arrays and
+ * raising a flag after a system fence, every pushed value travels with its epoch tag as two 8-byte words into
+ * a landing buffer of the neighbour (`peer_land[o]` = base of the buffer of the neighbour at offset o,
+ * `my_land` mine; 2 * 9 * land_len * 2 uint64 each, zero-initialised fabric memory, land_len >= max(nx, ny)),
+ * and the receiver polls each halo cell's own slot: one NVLink one-way latency per step, no fence round trip.
+ * `my_flags` is still needed for the error word. */
 int igg_diffusion2d_resident(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
                              double _dx, double _dy, int nsteps, double* const* peer_T, double* const* peer_T2,
                              uint64_t* const* peer_flags, uint64_t* my_flags, uint64_t epoch0,
+                             uint64_t* const* peer_land, uint64_t* my_land, int land_len,
                              int* cluster_size_out, void* stream);
 
 /* ---- 2-D diffusion, three-kernel form (reference scripts/diffusion_2D_kp.jl:16-54) ------------ */

@@ -24,6 +24,7 @@ reads back the step's diagnostic ``[max(T), sum(T)]`` (D2H into pinned memory).
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Sequence, Tuple
 
 import torch
@@ -81,6 +82,10 @@ class Diffusion2D:
         self._repoch = 0
         if mode == "resident":
             self._rflags = fabric_zeros((9 * 16 + 16,), torch.int64)      # per-(offset, CTA) epoch flags
+            # landing buffers of the low-latency exchange: [parity][offset][index along the edge][2 words]
+            self._rll = os.environ.get("IGG_RESIDENT_LL", "1") != "0"
+            self._rland_len = max(nx, ny)
+            self._rland = fabric_zeros((2 * 9 * self._rland_len * 2,), torch.int64) if self._rll else None
         self._gbar = torch.zeros(1, dtype=torch.int64, device=dev)
         self._gbar_base = 0
         self._running = False
@@ -160,15 +165,21 @@ class Diffusion2D:
             if n <= 0:
                 return
             fab = self.plan.fab
-            pT = pT2 = pF = None
+            pT = pT2 = pF = pL = None
             if fab.neighbors:
-                pT, pT2, pF = [0] * 9, [0] * 9, [0] * 9
+                pT, pT2, pF, pL = [0] * 9, [0] * 9, [0] * 9, [0] * 9
                 for (o, r) in fab.neighbors:
                     k = (o[0] + 1) * 3 + (o[1] + 1)
                     pT[k], pT2[k] = fab.peer_ptr(self.T, r), fab.peer_ptr(self.T2, r)
                     pF[k] = fab.peer_ptr(self._rflags, r)
+                    if self._rll:
+                        pL[k] = fab.peer_ptr(self._rland, r)
+                if not self._rll:
+                    pL = None
             native.diffusion2d_resident(self.T, self.T2, self.Cp, self.lam, self.dt, self._dx, self._dy, n, pT, pT2,
-                                        pF, self._rflags.data_ptr(), self._repoch + 1)
+                                        pF, self._rflags.data_ptr(), self._repoch + 1, pL,
+                                        self._rland.data_ptr() if (self._rll and pL is not None) else 0,
+                                        self._rland_len)
             self._repoch += n
             if n % 2:
                 self.T, self.T2 = self.T2, self.T

@@ -66,7 +66,7 @@ def _declare(lib) -> None:
                                  C.POINTER(Push2D), vp], i),
         "igg_diffusion2d_step_controlled": ([vp, vp, vp, i, i, vp, vp, vp, vp, vp, i, i, C.POINTER(Push2D), vp], i),
         "igg_diffusion2d_resident": ([vp, vp, vp, i, i, d, d, d, d, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), vp,
-                                     u64, C.POINTER(i), vp], i),
+                                     u64, C.POINTER(vp), vp, i, C.POINTER(i), vp], i),
         "igg_diffusion2d_run": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, i, C.POINTER(Push2D), C.POINTER(Push2D), vp], i),
         "igg_diffusion2d_multistep": ([vp, vp, vp, i, i, d, d, d, d, i, C.POINTER(Push2D), C.POINTER(vp), vp,
                                       C.c_ulonglong, C.POINTER(i), vp], i),
@@ -215,22 +215,26 @@ def diffusion2d_step_controlled(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Ten
 
 def diffusion2d_resident(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
                          _dy: float, nsteps: int, peer_T=None, peer_T2=None, peer_flags=None, my_flags: int = 0,
-                         epoch0: int = 0) -> int:
+                         epoch0: int = 0, peer_land=None, my_land: int = 0, land_len: int = 0) -> int:
     """``nsteps`` steps with the field resident in one thread-block cluster (``igg_diffusion2d_resident``).
 
     ``peer_T`` / ``peer_T2`` / ``peer_flags``: sequences of 9 raw pointers (0 = no neighbour) indexed
-    ``(ox+1)*3 + (oy+1)``, or ``None`` for a run without communication.  Returns the cluster size used."""
+    ``(ox+1)*3 + (oy+1)``, or ``None`` for a run without communication.  ``peer_land`` (9 raw pointers) +
+    ``my_land`` + ``land_len`` select the low-latency exchange (values travel with their epoch tag into
+    landing buffers).  Returns the cluster size used."""
     lib = require()
     nx, ny = T.shape
     csz = C.c_int(0)
-    if peer_flags is None:
-        a = b = f = None
-    else:
+    a = b = f = ld = None
+    if peer_flags is not None:
         a = (C.c_void_p * 9)(*[x or None for x in peer_T])
         b = (C.c_void_p * 9)(*[x or None for x in peer_T2])
         f = (C.c_void_p * 9)(*[x or None for x in peer_flags])
+    if peer_land is not None:
+        ld = (C.c_void_p * 9)(*[x or None for x in peer_land])
     _check(lib.igg_diffusion2d_resident(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
-                                        int(nsteps), a, b, f, my_flags or None, int(epoch0), C.byref(csz), _stream()))
+                                        int(nsteps), a, b, f, my_flags or None, int(epoch0), ld, my_land or None,
+                                        int(land_len), C.byref(csz), _stream()))
     return csz.value
 
 
