@@ -101,6 +101,8 @@ def diffusion3D(cfg: DiffusionConfig = None, finalize: bool = True) -> RunResult
     g = global_grid()
     if not cfg.quiet:
         print(f"Process {me} selecting device {g.device}", flush=True)
+    if g.device_type != "cuda":
+        return _diffusion3D_cpu(cfg, me, dims, nprocs, finalize)
     n0 = native.launch_count()
     s = Diffusion3D(cfg.nx, cfg.ny, cfg.nz, lx=cfg.lx, ly=cfg.ly, lz=cfg.lz, lam=cfg.lam, Cp0=cfg.Cp0,
                     mode="fused" if cfg.fused else "plain", variant=cfg.kernel, b_width=cfg.b_width,
@@ -132,6 +134,33 @@ def diffusion3D(cfg: DiffusionConfig = None, finalize: bool = True) -> RunResult
             res.raw, _ = save_raw(base, T_v, {"variant": "3D", "nprocs": nprocs, "dims": list(dims), "nt": nt})
     if finalize:
         detach_local(res)
+        finalize_global_grid()
+    return res
+
+
+def _diffusion3D_cpu(cfg: DiffusionConfig, me: int, dims, nprocs: int, finalize: bool) -> RunResult:
+    """Array-programming 3-D run on CPU tensors over gloo (plumbing / tests; same structure as the 2-D
+    ``ap`` application, reference ``scripts/diffusion_2D_ap.jl:37-43``)."""
+    shape = (cfg.nx, cfg.ny, cfg.nz)
+    dx, dy, dz = cfg.lx / nx_g(), cfg.ly / ny_g(), cfg.lz / nz_g()
+    dt = ref.time_step_3d(dx, dy, dz, cfg.Cp0, cfg.lam)
+    probe = torch.empty(shape, device="meta")
+    xs, ys, zs = (coords_g(d, h, probe) for d, h in enumerate((dx, dy, dz)))
+    T = ref.gaussian_ic_3d(xs, ys, zs, dx, dy, dz, cfg.lx, cfg.ly, cfg.lz)
+    Cp = cfg.Cp0 * torch.ones(shape, dtype=torch.float64)
+    for _ in range(int(cfg.nt)):
+        ref.ap_step_3d(T, Cp, cfg.lam, dt, dx, dy, dz)
+        update_halo(T)
+    res = RunResult("3D", me, nprocs, dims, int(cfg.nt), T_local=T)
+    if cfg.do_vis:
+        T_v = torch.zeros(tuple((n - 2) * d for n, d in zip(shape, dims)), dtype=torch.float64) if me == 0 else None
+        gather(inner(T).contiguous(), T_v)
+        if me == 0:
+            res.T_v, res.max_T = T_v, float(T_v.max())
+            base = os.path.join(cfg.outdir, output_name("3D", nprocs, nx_g(), ny_g(), nz_g()))
+            res.png = save_heatmap(base + ".png", T_v[:, :, T_v.shape[2] // 2], title="3D: mid-plane z slice")
+            res.raw, _ = save_raw(base, T_v, {"variant": "3D", "nprocs": nprocs, "dims": list(dims), "nt": int(cfg.nt)})
+    if finalize:
         finalize_global_grid()
     return res
 

@@ -37,7 +37,7 @@ def selectdevice_test(N: int = 4, transports=("peer", "nccl"), quiet: bool = Fal
     me, dims, nprocs, coords, _ = init_global_grid(4, 4, 1, dimy=1, periodx=1, quiet=True)
     g = global_grid()
     if g.device_type != "cuda":
-        raise RuntimeError("selectdevice_test needs CUDA devices")
+        transports = ("gloo",)          # CPU plumbing run: same ring, host buffers over gloo
     rank_l = local_rank()
     size = nprocs
     dst, src = (me + 1) % size, (me - 1) % size
@@ -67,13 +67,14 @@ def selectdevice_test(N: int = 4, transports=("peer", "nccl"), quiet: bool = Fal
             torch.cuda.synchronize()
             if int(flag[1]) != 0:
                 raise RuntimeError("peer flag wait timed out")
-        elif tr == "nccl":
+        elif tr in ("nccl", "gloo"):
             recv = torch.empty(N, dtype=torch.float64, device=g.device)
             if size > 1:
                 g.comm.exchange([(send, dst, 0)], [(recv, src, 0)])
             else:
                 recv.copy_(send)
-            torch.cuda.synchronize()
+            if g.device_type == "cuda":
+                torch.cuda.synchronize()
         else:
             raise ValueError(f"unknown transport {tr!r}")
         out[tr] = recv.cpu()

@@ -213,7 +213,7 @@ def oracle_2d(nx_g: int, ny_g: int, nt: int, form: str = "ap", lx: float = 10.0,
 
 
 def oracle_3d(nx_g: int, ny_g: int, nz_g: int, nt: int, lx=10.0, ly=10.0, lz=10.0, lam=1.0, Cp0=1.0,
-              dtype=torch.float64):
+              dtype=torch.float64, form: str = "perf"):
     dx, dy, dz = lx / nx_g, ly / ny_g, lz / nz_g
     dt = time_step_3d(dx, dy, dz, Cp0, lam)
     xs = torch.arange(nx_g, dtype=dtype) * dx
@@ -221,6 +221,10 @@ def oracle_3d(nx_g: int, ny_g: int, nz_g: int, nt: int, lx=10.0, ly=10.0, lz=10.
     zs = torch.arange(nz_g, dtype=dtype) * dz
     T = gaussian_ic_3d(xs, ys, zs, dx, dy, dz, lx, ly, lz)
     Cp = Cp0 * torch.ones_like(T)
+    if form == "ap":
+        for _ in range(nt):
+            ap_step_3d(T, Cp, lam, dt, dx, dy, dz)
+        return T, dt
     T2 = T.clone()
     for _ in range(nt):
         perf_step_3d(T2, T, Cp, lam, dt, 1.0 / dx, 1.0 / dy, 1.0 / dz)

@@ -31,3 +31,14 @@ def test_ap_app_8_ranks_4x2_layout(tmp_path):
 def test_grid_can_be_reinitialised_in_one_process():
     outs = run_workers("reinit_gloo.py", 2)
     assert all("ok" in o for o in outs)
+
+
+@pytest.mark.parametrize("nprocs", [4, 8])
+def test_kp_3d_and_hide_communication_over_gloo(nprocs, tmp_path):
+    outs = run_workers("apps_gloo.py", nprocs, (str(tmp_path), nprocs), timeout=600)
+    assert all("ok" in o for o in outs)
+
+
+def test_ring_smoke_test_over_gloo():
+    outs = run_workers("ring_gloo.py", 4)
+    assert all("ok" in o for o in outs)
