@@ -12,6 +12,8 @@
 extern "C" int igg_cpu_diffusion2d_step(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
                                         double dt, double _dx, double _dy) {
     if (!T || !T2 || !Cp || nx < 3 || ny < 3) return IGG_ERR_INVALID;
+    // rows are independent: OpenMP over ix when the library was built with it (IGG_CPU_THREADS / OMP_NUM_THREADS)
+#pragma omp parallel for schedule(static)
     for (int ix = 1; ix < nx - 1; ++ix) {
         const double* c = T + (size_t)ix * ny;
         const double* u = c - ny;

@@ -54,8 +54,8 @@ def _compile(src: str, force: bool, verbose: bool, hdr_m: float) -> str:
         return obj
     cmd = [nvcc(), *ARCH, *NVCC_FLAGS, "-c", src, "-o", obj]
     if src.endswith(".cpp"):
-        cmd = [nvcc(), "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-I", INC,
-               "-c", src, "-o", obj]
+        cmd = [nvcc(), "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off",
+               "-Xcompiler", "-fopenmp", "-I", INC, "-c", src, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = os.path.join(OBJ, os.path.basename(src) + ".log")
     with open(log, "w") as f:
@@ -76,7 +76,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         objs = list(ex.map(lambda s: _compile(s, force, verbose, hdr_m), srcs))
     newest = max(os.path.getmtime(o) for o in objs)
     if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < newest:
-        cmd = [nvcc(), *ARCH, "-shared", "-cudart", "static", "-o", LIB, *objs]
+        cmd = [nvcc(), *ARCH, "-shared", "-cudart", "static", "-Xcompiler", "-fopenmp", "-o", LIB, *objs]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
