@@ -84,3 +84,20 @@ def test_box_form_equals_sequential_form(nxyz, dims, periods):
         vg.update_halo_boxes(b)
         for r in range(vg.nprocs):
             assert torch.equal(a[r], b[r]), (shp, r)
+
+
+@pytest.mark.parametrize("overlaps", [(3, 3, 3), (2, 3, 2), (4, 2, 2)])
+def test_wider_overlaps_box_form_and_global_size(overlaps):
+    """overlaps > 2 (upstream keyword): plane indices shift, the box form still equals the sequential form."""
+    vg = VirtualGrid((9, 8), (3, 2), (0, 1), overlaps)
+    assert vg.nxyz_g[0] == 3 * (9 - overlaps[0]) + overlaps[0]
+    assert vg.nxyz_g[1] == 2 * (8 - overlaps[1])            # periodic: overlap not counted
+    specs = halo_planes((9, 8, 1), overlaps, (9, 8))
+    assert specs[0].send == (overlaps[0] - 1, 9 - overlaps[0]) and specs[0].recv == (0, 8)
+    gen = torch.Generator().manual_seed(11)
+    a = [torch.rand(9, 8, generator=gen, dtype=torch.float64) for _ in range(vg.nprocs)]
+    b = [t.clone() for t in a]
+    vg.update_halo(a)
+    vg.update_halo_boxes(b)
+    for r in range(vg.nprocs):
+        assert torch.equal(a[r], b[r])
