@@ -333,6 +333,9 @@ class PushPlan:
         self.ndim = fields[0].dim()
         if self.ndim not in (2, 3):
             raise ValueError("PushPlan supports 2-D and 3-D fields")
+        if any(g.overlaps[d] != 2 for d in range(self.ndim)):
+            # the in-kernel push sends index 1 / n-2 into index n-1 / 0: overlap 2, halo width 1
+            raise ValueError("the fused push needs overlaps == 2; use update_halo() for wider overlaps")
         for A in fields:
             if tuple(A.shape) != tuple(g.nxyz[:self.ndim]):
                 raise ValueError("pushed fields must have the local grid size (no staggering)")
