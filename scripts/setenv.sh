@@ -13,5 +13,9 @@ export IGG_B200_TRANSPORT=${IGG_B200_TRANSPORT:-peer}
 # Kernel tuning knobs (defaults are the measured best on B200; see profiles/):
 #   IGG_TMA_RPT    4  = rows per consumer thread (16 consumer warps + 1 producer warp per CTA)
 #   IGG_TILE_BAND  0  = row-major tile order (N > 0: bands of N tile columns)
-#   IGG_L2_PROMO   2  = 128-byte L2 promotion for TMA loads
+#   IGG_L2_PROMO   1  = 64-byte L2 promotion for TMA loads (0 none, 2 128 B, 3 256 B)
+#   IGG_TMA_STRIP  1  = whole-interior steps of grids with nx >= 512 use the strip-marching kernel (0: tiles)
+#   IGG_STRIP_ROWS 256 = rows per work item of the strip-marching kernel (multiple of 32)
+#   IGG_RESIDENT_LL 1 = cluster-resident kernel exchanges halos as value+epoch-tag words (0: fence + flag)
+#   IGG_E2E_SPIN   1  = step_controlled waits by polling an event (0: cudaStreamSynchronize)
 echo "ENV setup done (transport: $IGG_B200_TRANSPORT)"
