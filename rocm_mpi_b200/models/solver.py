@@ -93,12 +93,7 @@ class Diffusion2D:
         # streams for the hide structure (reference perf_hide.jl:63-68: HIGH / LOW priority queues)
         self._s_hi = self._s_lo = None
         if mode == "hide":
-            lo_p, hi_p = -1, 0
-            try:
-                lo_p, hi_p = torch.cuda.Stream.priority_range()
-            except Exception:
-                pass
-            self._s_hi = torch.cuda.Stream(device=dev, priority=-1)
+            self._s_hi = torch.cuda.Stream(device=dev, priority=-1)      # -1 = high, 0 = default
             self._s_lo = torch.cuda.Stream(device=dev, priority=0)
             self._ev_hi = torch.cuda.Event()
             self._ev_lo = torch.cuda.Event()
