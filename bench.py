@@ -36,7 +36,7 @@ def parse_args():
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=50)
     p.add_argument("--warmup", type=int, default=10)
-    p.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl", "nccl_tma", "plain_peer", "hide", "direct"])
+    p.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl", "nccl_tma", "plain_peer", "hide", "direct", "temporal"])
     p.add_argument("--nx", type=int, default=16384)
     p.add_argument("--ny", type=int, default=16384)
     p.add_argument("--b-width", type=int, nargs=2, default=[16, 4])
@@ -124,6 +124,7 @@ def main() -> int:
     g = igg.global_grid()
     mode, variant, transport = {"ours": ("fused", "tma", "peer"), "hide": ("hide", "tma", "peer"),
                                 "direct": ("fused", "direct", "peer"),
+                                "temporal": ("temporal", "tma", "peer"),   # experimental: two steps per pass
                                 "plain_peer": ("plain", "tma", "peer"), "nccl_tma": ("plain", "tma", "nccl"),
                                 "nccl": ("plain", "direct", "nccl")}[a.impl]
     s = Diffusion2D(nx, ny, mode=mode, variant=variant, transport=transport, b_width=a.b_width)

@@ -1,0 +1,370 @@
+// 2-D heat diffusion, TWO time steps per pass over memory, for sm_100a.
+//
+// The reference does one step per launch and per trip through HBM (scripts/diffusion_2D_perf.jl:47-52); its
+// metric T_eff = 3*nx*ny*8 B / t_it (scripts/diffusion_2D_perf.jl:55-58) is therefore capped by the memory
+// bandwidth.  This kernel keeps step k+1 in shared memory and writes only step k+2, so t_it per step drops
+// towards half a memory pass.  No counterpart in the reference.
+//
+// Structure (same skeleton as the strip kernel in stencil2d.cu): one persistent CTA per SM; a producer warp
+// streams 16-row x 128-column blocks of T and of Cp through mbarrier rings with TMA; the consumer warps
+//   step 1  block b of T  ->  block b of the mid ring          (shared -> shared)
+//   bar.sync among consumers
+//   step 2  mid blocks b-1, b  ->  T2 rows one behind the block (shared -> global, streaming stores)
+// The index arithmetic of both steps lives in temporal2d_core.h and is executed unchanged by the host
+// emulator that the CPU tests run.
+//
+// Multi-GPU (halo width 1 is kept, so step k+1 of the neighbours' edge cells is needed half way):
+//   igg_diffusion2d_midlines   small kernel: waits for the neighbours' pushes of the previous pass, computes
+//                              step k+1 on this rank's four send lines and stores them into the neighbours'
+//                              mid-line buffers, then releases the mid flag of this pass;
+//   igg_diffusion2d_step2      the pass: items that read a mid line first acquire that neighbour's mid flag;
+//                              step-k+2 edge cells are pushed into the neighbours' halo cells and the DATA
+//                              flag of the epoch is released exactly as in the one-step kernel (push.cuh).
+// The two kernels of a rank run in stream order; waits only ever target OTHER ranks' kernels.
+#include <stdlib.h>
+#include <string.h>
+
+#include "push.cuh"
+#include "temporal2d_core.h"
+
+namespace {
+
+using namespace igg;
+using namespace igg_t2;
+
+constexpr int T2_SMEM_BYTES = (SNT + SNC + SNM) * BLK_BYTES + 256;
+
+struct T2Params {
+    double* T2;
+    Geom g;
+    Phys ph;
+    const double* dev_params;      // optional {lam, dt, _dx, _dy} in device memory
+    MidLines ml;
+    const uint64_t* mid_flag[4];   // my mid flags, one per line (xlo, xhi, ylo, yhi); NULL = no neighbour
+    int has_push;
+    int edge_tiles[9];
+    int side_nb[4];
+    igg_push2d push;
+};
+
+__device__ __forceinline__ void mbar_arrive_(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void consumer_sync_(int nthreads) {
+    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
+}
+
+template <int RPT>
+__global__ void __launch_bounds__(NPAIR*(SRB / RPT) + 32, 1)
+diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapC,
+                        const __grid_constant__ T2Params p) {
+    constexpr int CONSUMERS = NPAIR * (SRB / RPT);
+    constexpr int NCW = CONSUMERS / 32;
+    extern __shared__ __align__(128) unsigned char smem[];
+    double* ringT = reinterpret_cast<double*>(smem);
+    double* ringC = ringT + SNT * BLK;
+    double* ringM = ringC + SNC * BLK;
+    uint64_t* fullT = reinterpret_cast<uint64_t*>(ringM + SNM * BLK);
+    uint64_t* emptyT = fullT + SNT;
+    uint64_t* fullC = emptyT + SNT;
+    uint64_t* emptyC = fullC + SNC;
+    const int tid = threadIdx.x;
+    const int first = blockIdx.x;
+    const int nitems = num_items(p.g);
+    const int n_my = first < nitems ? (nitems - first + gridDim.x - 1) / gridDim.x : 0;
+    if (tid == 0) {
+        for (int s = 0; s < SNT; ++s) { mbar_init(&fullT[s], 1); mbar_init(&emptyT[s], NCW); }
+        for (int s = 0; s < SNC; ++s) { mbar_init(&fullC[s], 1); mbar_init(&emptyC[s], NCW); }
+        fence_mbar_init();
+    }
+    __syncthreads();
+    const int nx = p.g.nx, ny = p.g.ny;
+
+    if (tid >= CONSUMERS) {
+        // ===== producer ===================================================================================
+        if (tid == CONSUMERS) {
+            tma_prefetch_desc(&mapT);
+            tma_prefetch_desc(&mapC);
+            unsigned tq = 0, cq = 0;
+            for (int k = 0; k < n_my; ++k) {
+                const Item it = make_item(p.g, first + k * gridDim.x);
+                if (p.has_push) {
+                    // mid lines this item may read: acquire the neighbours' mid flag of this pass
+                    const int x_last = it.xin0 + it.nbi * SRB - 1;
+                    if (it.xin0 <= 0 && p.mid_flag[0]) wait_flag_ge(p.mid_flag[0], p.push.epoch, p.push.err_word);
+                    if (x_last >= nx - 1 && p.mid_flag[1]) wait_flag_ge(p.mid_flag[1], p.push.epoch, p.push.err_word);
+                    if (it.yb <= 0 && p.mid_flag[2]) wait_flag_ge(p.mid_flag[2], p.push.epoch, p.push.err_word);
+                    if (it.yb + BW - 1 >= ny - 1 && p.mid_flag[3])
+                        wait_flag_ge(p.mid_flag[3], p.push.epoch, p.push.err_word);
+                }
+                auto issue_T = [&](int b) {
+                    const unsigned s = tq % SNT;
+                    if (tq >= SNT) mbar_wait(&emptyT[s], ((tq / SNT) - 1) & 1);
+                    mbar_arrive_expect_tx(&fullT[s], BLK_BYTES);
+                    tma_load_2d(ringT + s * BLK, &mapT, &fullT[s], it.yb, it.xin0 + b * SRB);
+                    ++tq;
+                };
+                auto issue_C = [&](int b) {
+                    const unsigned s = cq % SNC;
+                    if (cq >= SNC) mbar_wait(&emptyC[s], ((cq / SNC) - 1) & 1);
+                    mbar_arrive_expect_tx(&fullC[s], BLK_BYTES);
+                    tma_load_2d(ringC + s * BLK, &mapC, &fullC[s], it.yb, it.xin0 + b * SRB);
+                    ++cq;
+                };
+                issue_T(0);
+                for (int b = 0; b < it.nbi; ++b) {
+                    if (b + 1 < it.nbi) issue_T(b + 1);
+                    issue_C(b);
+                }
+            }
+        }
+        return;
+    }
+
+    // ===== consumers ====================================================================================
+    const int cp = tid % NPAIR;   // column pair
+    const int rg = tid / NPAIR;   // row group inside a block
+    Phys ph = p.ph;
+    if (p.dev_params) {
+        ph.lam = p.dev_params[0];
+        ph.dt = p.dev_params[1];
+        ph._dx = p.dev_params[2];
+        ph._dy = p.dev_params[3];
+    }
+    unsigned tq = 0, cq = 0, mq = 0;
+
+    for (int k = 0; k < n_my; ++k) {
+        const Item it = make_item(p.g, first + k * gridDim.x);
+        const bool e_xl = it.ci == 0 && p.side_nb[0], e_xh = it.ci == p.g.nti - 1 && p.side_nb[1];
+        const bool e_yl = it.j == 0 && p.side_nb[2], e_yh = it.j == p.g.ntj - 1 && p.side_nb[3];
+        const bool edge_tile = p.has_push && (e_xl || e_xh || e_yl || e_yh);
+        const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;      // inside [1, nx-2] by construction
+        const int y = it.yb + 2 * cp;
+        mbar_wait(&fullT[tq % SNT], (tq / SNT) & 1);
+        for (int b = 0; b < it.nbi; ++b) {
+            const unsigned qb = tq + b, qc = cq + b, qm = mq + b;
+            if (b + 1 < it.nbi) mbar_wait(&fullT[(qb + 1) % SNT], ((qb + 1) / SNT) & 1);
+            mbar_wait(&fullC[qc % SNC], (qc / SNC) & 1);
+            const double* curT = ringT + (qb % SNT) * BLK;
+            const double* prevT = b > 0 ? ringT + ((qb + SNT - 1) % SNT) * BLK : curT;
+            const double* nextT = b + 1 < it.nbi ? ringT + ((qb + 1) % SNT) * BLK : curT;
+            const double* curC = ringC + (qc % SNC) * BLK;
+            const double* prevC = b > 0 ? ringC + ((qc + SNC - 1) % SNC) * BLK : curC;
+            double* curM = ringM + (qm % SNM) * BLK;
+            const double* prevM = ringM + ((qm + SNM - 1) % SNM) * BLK;
+            const int xb = it.xin0 + b * SRB;
+
+            step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, nx, ny, ph, p.ml);
+            __syncwarp();
+            if ((tid & 31) == 0 && b > 0) mbar_arrive_(&emptyT[(qb + SNT - 1) % SNT]);   // T block b-1 is done
+            consumer_sync_(CONSUMERS);                                                   // mid block b complete
+
+            double oA[RPT], oB[RPT];
+            unsigned wA, wB;
+            step2_rows<RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, ny, ph, oA, oB, wA, wB);
+#pragma unroll
+            for (int r = 0; r < RPT; ++r) {
+                const bool a = (wA >> r) & 1u, c = (wB >> r) & 1u;
+                if (a | c) {
+                    const int x = xb - 1 + rg * RPT + r;
+                    double* out = p.T2 + (size_t)x * ny + y;
+                    if (a && c) {
+                        st_cs_f64x2(out, oA[r], oB[r]);
+                    } else {
+                        if (a) st_cs_f64(out, oA[r]);
+                        if (c) st_cs_f64(out + 1, oB[r]);
+                    }
+                    if (edge_tile) {
+                        if (a) push_cell_2d(p.push, nx, ny, x, y, oA[r]);
+                        if (c) push_cell_2d(p.push, nx, ny, x, y + 1, oB[r]);
+                    }
+                }
+            }
+            __syncwarp();
+            if ((tid & 31) == 0 && b > 0) mbar_arrive_(&emptyC[(qc + SNC - 1) % SNC]);   // Cp block b-1 is done
+        }
+        __syncwarp();
+        if ((tid & 31) == 0) {
+            mbar_arrive_(&emptyT[(tq + it.nbi - 1) % SNT]);
+            mbar_arrive_(&emptyC[(cq + it.nbi - 1) % SNC]);
+        }
+        tq += it.nbi;
+        cq += it.nbi;
+        mq += it.nbi;
+        if (edge_tile) {
+            consumer_sync_(CONSUMERS);   // every remote store of this item has been issued
+            if (tid == 0) signal_edges_2d(p.push, p.edge_tiles, e_xl, e_xh, e_yl, e_yh);
+        }
+    }
+}
+
+// ---- mid lines -------------------------------------------------------------------------------------------
+struct MidParams {
+    const double* T;
+    const double* Cp;
+    int nx, ny;
+    Phys ph;
+    const double* dev_params;
+    igg_mid2d mid;
+    const uint64_t* data_flag[4];   // DATA flags of the four face neighbours (previous pass), NULL = none
+    uint64_t* err_word;
+    uint64_t epoch;
+};
+
+constexpr int MID_CTAS_PER_FACE = 8;
+
+__global__ void __launch_bounds__(256) diff2d_midlines_kernel(const __grid_constant__ MidParams p) {
+    const int face = blockIdx.y;
+    if (p.mid.peer_mid[face] == nullptr) return;
+    // the cells read here include halo cells of all four sides: wait for every face neighbour's pushes of
+    // the previous pass
+    if (threadIdx.x < 4 && p.data_flag[threadIdx.x])
+        wait_flag_ge(p.data_flag[threadIdx.x], p.epoch - 1, p.err_word);
+    __syncthreads();
+    Phys ph = p.ph;
+    if (p.dev_params) {
+        ph.lam = p.dev_params[0];
+        ph.dt = p.dev_params[1];
+        ph._dx = p.dev_params[2];
+        ph._dy = p.dev_params[3];
+    }
+    const int n = face_length(face, p.nx, p.ny);
+    double* dst = p.mid.peer_mid[face] + mid_line_offset(mid_line_of_face(face), p.nx, p.ny);
+    for (int i = 1 + blockIdx.x * blockDim.x + threadIdx.x; i <= n - 2; i += gridDim.x * blockDim.x)
+        dst[i] = mid_line_value(p.T, p.Cp, p.nx, p.ny, face, i, ph);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned long long old = atomicAdd((unsigned long long*)p.mid.my_count[face], 1ull);
+        if ((old + 1ull) % (unsigned long long)gridDim.x == 0ull) {
+            __threadfence_system();
+            st_release_sys(p.mid.peer_flag[face], p.epoch);
+        }
+    }
+}
+
+static int env_int_(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+template <int RPT>
+static int launch_t2(const CUtensorMap& mT, const CUtensorMap& mC, const T2Params& p, cudaStream_t st) {
+    auto kern = diff2d_temporal2_kernel<RPT>;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    IGG_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    const int sms = igg::sm_count();
+    const int nitems = num_items(p.g);
+    const int grid = nitems < sms ? nitems : sms;
+    kern<<<grid, NPAIR*(SRB / RPT) + 32, T2_SMEM_BYTES, st>>>(mT, mC, p);
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int igg_temporal2d_default_rows(void) {
+    static int v = -1;
+    if (v < 0) {
+        v = env_int_("IGG_T2_ROWS", 252);
+        if (v < SRB - 4 || (v + 4) % SRB) v = 252;
+    }
+    return v;
+}
+
+extern "C" int igg_diffusion2d_step2(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
+                                     double dt, double _dx, double _dy, const double* dev_params,
+                                     const igg_push2d* push, const igg_mid2d* mid, void* stream) {
+    IGG_REQUIRE(T && T2 && Cp, "igg_diffusion2d_step2: null field pointer");
+    IGG_REQUIRE(nx >= 3 && ny >= 4, "igg_diffusion2d_step2: need nx >= 3, ny >= 4 (got %d x %d)", nx, ny);
+    IGG_REQUIRE((push == nullptr) == (mid == nullptr),
+                "igg_diffusion2d_step2: push and mid descriptors come together (or both NULL)");
+    if ((ny & 1) || (((uintptr_t)T | (uintptr_t)T2 | (uintptr_t)Cp) & 15)) {
+        igg::set_error("igg_diffusion2d_step2: needs even ny and 16-byte aligned fields (ny=%d)", ny);
+        return IGG_ERR_UNSUPPORTED;
+    }
+    T2Params p;
+    memset(&p, 0, sizeof(p));
+    p.T2 = T2;
+    p.g = make_geom(nx, ny, igg_temporal2d_default_rows(), push ? 1 : 0);
+    p.ph.lam = lam; p.ph.dt = dt; p.ph._dx = _dx; p.ph._dy = _dy;
+    p.dev_params = dev_params;
+    p.has_push = push ? 1 : 0;
+    for (int sx = -1; sx <= 1; ++sx)
+        for (int sy = -1; sy <= 1; ++sy)
+            p.edge_tiles[(sx + 1) * 3 + (sy + 1)] = (sx != 0 && sy != 0) ? 1 : (sx != 0 ? p.g.ntj : p.g.nti);
+    if (push) {
+        IGG_REQUIRE(push->epoch >= 1, "igg_diffusion2d_step2: push epoch must be >= 1");
+        p.push = *push;
+        for (int sx = -1; sx <= 1; ++sx)
+            for (int sy = -1; sy <= 1; ++sy) {
+                if (!push->peer_dst[(sx + 1) * 3 + (sy + 1)]) continue;
+                if (sx == -1) p.side_nb[0] = 1;
+                if (sx == 1) p.side_nb[1] = 1;
+                if (sy == -1) p.side_nb[2] = 1;
+                if (sy == 1) p.side_nb[3] = 1;
+            }
+        // line l of my buffer is filled by the neighbour on that side (xlo by the x-low neighbour, ...)
+        const int face_slot[4] = {0 * 3 + 1, 2 * 3 + 1, 1 * 3 + 0, 1 * 3 + 2};
+        const double* base = mid->my_mid;
+        IGG_REQUIRE(base != nullptr, "igg_diffusion2d_step2: mid->my_mid is NULL");
+        for (int l = 0; l < 4; ++l) {
+            const bool nb = push->peer_dst[face_slot[l]] != nullptr;
+            p.mid_flag[l] = nb ? mid->my_flag[l] : nullptr;
+            IGG_REQUIRE(!nb || mid->my_flag[l], "igg_diffusion2d_step2: mid flag missing for an existing neighbour");
+        }
+        p.ml.xlo = p.mid_flag[0] ? base + mid_line_offset(0, nx, ny) : nullptr;
+        p.ml.xhi = p.mid_flag[1] ? base + mid_line_offset(1, nx, ny) : nullptr;
+        p.ml.ylo = p.mid_flag[2] ? base + mid_line_offset(2, nx, ny) : nullptr;
+        p.ml.yhi = p.mid_flag[3] ? base + mid_line_offset(3, nx, ny) : nullptr;
+    }
+    CUtensorMap mT, mC;
+    const uint64_t dims[2] = {(uint64_t)ny, (uint64_t)nx};
+    const uint32_t box[2] = {BW, SRB};
+    int rc = igg::get_tensor_map_f64(T, 2, dims, box, &mT);
+    if (rc) return rc;
+    rc = igg::get_tensor_map_f64(Cp, 2, dims, box, &mC);
+    if (rc) return rc;
+    static int rpt = -1;
+    if (rpt < 0) rpt = env_int_("IGG_T2_RPT", 2);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (rpt == 4) rc = launch_t2<4>(mT, mC, p, st);
+    else rc = launch_t2<2>(mT, mC, p, st);
+    if (rc) return rc;
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int igg_diffusion2d_midlines(const double* T, const double* Cp, int nx, int ny, double lam, double dt,
+                                        double _dx, double _dy, const double* dev_params, const igg_push2d* push,
+                                        const igg_mid2d* mid, void* stream) {
+    IGG_REQUIRE(T && Cp && push && mid, "igg_diffusion2d_midlines: null argument");
+    IGG_REQUIRE(nx >= 3 && ny >= 3, "igg_diffusion2d_midlines: need nx, ny >= 3");
+    IGG_REQUIRE(push->epoch >= 1, "igg_diffusion2d_midlines: push epoch must be >= 1");
+    MidParams p;
+    memset(&p, 0, sizeof(p));
+    p.T = T; p.Cp = Cp; p.nx = nx; p.ny = ny;
+    p.ph.lam = lam; p.ph.dt = dt; p.ph._dx = _dx; p.ph._dy = _dy;
+    p.dev_params = dev_params;
+    p.mid = *mid;
+    const int face_slot[4] = {0 * 3 + 1, 2 * 3 + 1, 1 * 3 + 0, 1 * 3 + 2};
+    bool any = false;
+    for (int f = 0; f < 4; ++f) {
+        p.data_flag[f] = push->peer_dst[face_slot[f]] ? push->my_flag[face_slot[f]] : nullptr;
+        if (mid->peer_mid[f]) {
+            IGG_REQUIRE(mid->peer_flag[f] && mid->my_count[f], "igg_diffusion2d_midlines: incomplete mid descriptor");
+            any = true;
+        }
+    }
+    p.err_word = push->err_word;
+    p.epoch = push->epoch;
+    if (!any) return 0;
+    dim3 grid(MID_CTAS_PER_FACE, 4);
+    diff2d_midlines_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,128 @@
+// Host emulation of the two-steps-per-pass kernel (temporal2d.cu).
+//
+// The kernel's index arithmetic -- work items, ring slots, the two per-thread row loops and their masks --
+// lives in temporal2d_core.h and is compiled here for the CPU, so the tests can run exactly that code without
+// a GPU: a "worker" plays one persistent CTA with its own ring counters, the TMA box load is a copy with zero
+// fill, and the consumer barrier between step 1 and step 2 becomes two loops over the threads.
+// No counterpart in the reference (it has neither native code nor a multi-step kernel).
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "../include/igg_b200.h"
+#include "temporal2d_core.h"
+
+using namespace igg_t2;
+
+namespace {
+
+// what cp.async.bulk.tensor does for a [SRB x BW] box at (x, y): out-of-range elements read as zero
+void load_box(const double* A, int nx, int ny, int x, int y, double* dst) {
+    for (int r = 0; r < SRB; ++r) {
+        const int gx = x + r;
+        for (int c = 0; c < BW; ++c) {
+            const int gy = y + c;
+            dst[r * BW + c] = (gx >= 0 && gx < nx && gy >= 0 && gy < ny) ? A[(size_t)gx * ny + gy] : 0.0;
+        }
+    }
+}
+
+template <int RPT>
+void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const Phys& ph, int workers,
+             const MidLines& ml) {
+    constexpr int NRG = SRB / RPT;
+    const int nitems = num_items(g);
+    // 16-byte aligned rings, poisoned so that a read of a slot that was never filled shows up
+    std::vector<d2> bufT(SNT * BLK / 2), bufC(SNC * BLK / 2), bufM(SNM * BLK / 2);
+    double* ringT = reinterpret_cast<double*>(bufT.data());
+    double* ringC = reinterpret_cast<double*>(bufC.data());
+    double* ringM = reinterpret_cast<double*>(bufM.data());
+    for (int w = 0; w < workers; ++w) {
+        for (int i = 0; i < SNT * BLK; ++i) ringT[i] = 1e300;
+        for (int i = 0; i < SNC * BLK; ++i) ringC[i] = 1e300;
+        for (int i = 0; i < SNM * BLK; ++i) ringM[i] = 1e300;
+        unsigned tq = 0, cq = 0, mq = 0;
+        const int n_my = w < nitems ? (nitems - w + workers - 1) / workers : 0;
+        for (int k = 0; k < n_my; ++k) {
+            const Item it = make_item(g, w + k * workers);
+            const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;
+            load_box(T, g.nx, g.ny, it.xin0, it.yb, ringT + (tq % SNT) * BLK);
+            for (int b = 0; b < it.nbi; ++b) {
+                const unsigned qb = tq + b, qc = cq + b, qm = mq + b;
+                if (b + 1 < it.nbi)
+                    load_box(T, g.nx, g.ny, it.xin0 + (b + 1) * SRB, it.yb, ringT + ((qb + 1) % SNT) * BLK);
+                load_box(Cp, g.nx, g.ny, it.xin0 + b * SRB, it.yb, ringC + (qc % SNC) * BLK);
+                const double* curT = ringT + (qb % SNT) * BLK;
+                const double* prevT = b > 0 ? ringT + ((qb + SNT - 1) % SNT) * BLK : curT;
+                const double* nextT = b + 1 < it.nbi ? ringT + ((qb + 1) % SNT) * BLK : curT;
+                const double* curC = ringC + (qc % SNC) * BLK;
+                const double* prevC = b > 0 ? ringC + ((qc + SNC - 1) % SNC) * BLK : curC;
+                double* curM = ringM + (qm % SNM) * BLK;
+                const double* prevM = ringM + ((qm + SNM - 1) % SNM) * BLK;
+                const int xb = it.xin0 + b * SRB;
+                for (int rg = 0; rg < NRG; ++rg)
+                    for (int cp = 0; cp < NPAIR; ++cp)
+                        step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, g.nx, g.ny, ph, ml);
+                // ---- consumer barrier ----
+                for (int rg = 0; rg < NRG; ++rg)
+                    for (int cp = 0; cp < NPAIR; ++cp) {
+                        double oA[RPT], oB[RPT];
+                        unsigned wA, wB;
+                        step2_rows<RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, g.ny, ph, oA, oB,
+                                        wA, wB);
+                        const int y = it.yb + 2 * cp;
+                        for (int r = 0; r < RPT; ++r) {
+                            const int x = xb - 1 + rg * RPT + r;
+                            if ((wA >> r) & 1u) T2[(size_t)x * g.ny + y] = oA[r];
+                            if ((wB >> r) & 1u) T2[(size_t)x * g.ny + y + 1] = oB[r];
+                        }
+                    }
+            }
+            tq += it.nbi;
+            cq += it.nbi;
+            mq += it.nbi;
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" int igg_cpu_temporal2d_emulate(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
+                                          double dt, double _dx, double _dy, int scx, int rpt, int workers,
+                                          const double* mid_lines, int side_mask) {
+    if (!T || !T2 || !Cp || nx < 3 || ny < 4 || (ny & 1)) return IGG_ERR_INVALID;
+    if (scx < SRB - 4 || (scx + 4) % SRB || workers < 1 || (rpt != 2 && rpt != 4)) return IGG_ERR_INVALID;
+    if (side_mask && !mid_lines) return IGG_ERR_INVALID;
+    const Geom g = make_geom(nx, ny, scx, side_mask ? 1 : 0);
+    Phys ph;
+    ph.lam = lam;
+    ph.dt = dt;
+    ph._dx = _dx;
+    ph._dy = _dy;
+    MidLines ml;
+    ml.xlo = (side_mask & 1) ? mid_lines + mid_line_offset(0, nx, ny) : nullptr;
+    ml.xhi = (side_mask & 2) ? mid_lines + mid_line_offset(1, nx, ny) : nullptr;
+    ml.ylo = (side_mask & 4) ? mid_lines + mid_line_offset(2, nx, ny) : nullptr;
+    ml.yhi = (side_mask & 8) ? mid_lines + mid_line_offset(3, nx, ny) : nullptr;
+    if (rpt == 4) emulate<4>(T, T2, Cp, g, ph, workers, ml);
+    else emulate<2>(T, T2, Cp, g, ph, workers, ml);
+    return 0;
+}
+
+extern "C" int igg_cpu_temporal2d_midlines(const double* T, const double* Cp, int nx, int ny, double lam, double dt,
+                                           double _dx, double _dy, double* const* peer_mid) {
+    if (!T || !Cp || !peer_mid || nx < 3 || ny < 3) return IGG_ERR_INVALID;
+    Phys ph;
+    ph.lam = lam;
+    ph.dt = dt;
+    ph._dx = _dx;
+    ph._dy = _dy;
+    for (int face = 0; face < 4; ++face) {
+        if (!peer_mid[face]) continue;
+        const int n = face_length(face, nx, ny);
+        double* dst = peer_mid[face] + mid_line_offset(mid_line_of_face(face), nx, ny);
+        for (int i = 1; i <= n - 2; ++i) dst[i] = mid_line_value(T, Cp, nx, ny, face, i, ph);
+    }
+    return 0;
+}

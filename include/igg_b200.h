@@ -125,6 +125,47 @@ int igg_diffusion2d_resident(double* T, double* T2, const double* Cp, int nx, in
                              uint64_t* const* peer_land, uint64_t* my_land, int land_len,
                              int* cluster_size_out, void* stream);
 
+/* ---- 2-D diffusion, two steps per pass over memory (no reference counterpart: its loop,
+ *      scripts/diffusion_2D_perf.jl:47-52, makes one trip through memory per step) -----------------
+ * T2 <- two steps applied to T; step k+1 only ever exists in shared memory.  Boundary cells of T2 are never
+ * written, so T2 must already hold T's boundary values (true for any T2 that started as a copy of T).
+ * Needs even ny and 16-byte aligned fields (IGG_ERR_UNSUPPORTED otherwise).  `dev_params`: optional device
+ * array {lam, dt, _dx, _dy}.
+ * Multi-GPU: halo width stays 1, so the neighbours' step-(k+1) edge values are needed half way.  Per pass:
+ *   igg_diffusion2d_midlines(T, ...)   waits for the neighbours' pushes of epoch-1, computes step k+1 on this
+ *                                       rank's four send lines, stores them into the neighbours' mid-line
+ *                                       buffers and releases the mid flag `epoch`;
+ *   igg_diffusion2d_step2(T, T2, ...)   items that read a mid line acquire the mid flag `epoch` first; the
+ *                                       step-(k+2) edge cells are pushed into the neighbours' T2 and the DATA
+ *                                       flag `epoch` is released as igg_diffusion2d_step does.
+ * Both take the SAME push descriptor (one epoch per pass).  Sides are indexed x-low, x-high, y-low, y-high.
+ * STATUS: compiled and checked through its host emulator (igg_cpu_temporal2d_*); not yet run on a GPU. */
+typedef struct igg_mid2d {
+    const double* my_mid;           /* my mid-line buffer, 2*ny + 2*nx doubles: [xlo | xhi | ylo | yhi]      */
+    double* peer_mid[4];            /* mid-line buffer of the neighbour on side s (peer-mapped); NULL = none */
+    uint64_t* peer_flag[4];         /* mid flag in the pad of the neighbour on side s that this rank releases */
+    uint64_t* my_flag[4];           /* mid flag in MY pad that the neighbour on side s releases              */
+    uint64_t* my_count[4];          /* private CTA arrival counters (monotonic)                              */
+} igg_mid2d;
+#define IGG_SLOT_MID 56             /* flag pad: mid flags of sides 0..3; counter pad: their CTA counters     */
+int igg_diffusion2d_step2(const double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
+                          double _dx, double _dy, const double* dev_params, const igg_push2d* push,
+                          const igg_mid2d* mid, void* stream);
+int igg_diffusion2d_midlines(const double* T, const double* Cp, int nx, int ny, double lam, double dt, double _dx,
+                             double _dy, const double* dev_params, const igg_push2d* push, const igg_mid2d* mid,
+                             void* stream);
+/* output rows per work item of igg_diffusion2d_step2 (IGG_T2_ROWS, default 252) */
+int igg_temporal2d_default_rows(void);
+/* Host emulation of igg_diffusion2d_step2 that executes the kernel's own index code (csrc/temporal2d_core.h)
+ * thread by thread: `workers` plays gridDim.x, `rpt` the rows per thread (2 or 4), `scx` the rows per work item
+ * ((scx + 4) % 16 == 0).  `mid_lines`: this rank's mid-line buffer or NULL; `side_mask` bit s = a neighbour
+ * exists on side s.  igg_cpu_temporal2d_midlines fills the neighbours' buffers (`peer_mid[s]`, NULL = none). */
+int igg_cpu_temporal2d_emulate(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
+                               double dt, double _dx, double _dy, int scx, int rpt, int workers,
+                               const double* mid_lines, int side_mask);
+int igg_cpu_temporal2d_midlines(const double* T, const double* Cp, int nx, int ny, double lam, double dt,
+                                double _dx, double _dy, double* const* peer_mid);
+
 /* ---- 2-D diffusion, three-kernel form (reference scripts/diffusion_2D_kp.jl:16-54) ------------ */
 int igg_flux2d(double* qx, double* qy, const double* T, int nx, int ny, double lam, double _dx,
                double _dy, void* stream);

@@ -15,6 +15,9 @@ offers three ways to advance, all producing the same field:
 ``resident``  for grids that fit in the shared memory of one thread-block cluster (up to ~256 x 256): the
            field stays in shared memory for all ``n`` steps of a ``step(n)`` call; CTAs exchange rows through
            distributed shared memory and cluster barriers, GPUs through peer stores and per-CTA flags.
+``temporal``  EXPERIMENTAL (validated through its host emulator only, not yet on a GPU): two steps per pass
+           over memory -- step k+1 lives in shared memory only -- with the neighbours' step-(k+1) edge lines
+           sent half way by a small kernel; an odd last step falls back to the fused kernel.
 ``plain``  the reference's serial structure (``scripts/diffusion_2D_perf.jl:49-51``): full kernel,
            swap, ``update_halo(T)`` over the chosen transport (``nccl`` = the same-box baseline).
 
@@ -47,8 +50,10 @@ class Diffusion2D:
             raise RuntimeError("Diffusion2D runs on CUDA devices; use models.diffusion2d_ap on CPU")
         if (nx, ny) != tuple(g.nxyz[:2]):
             raise ValueError("nx, ny must be the local sizes given to init_global_grid")
-        if mode not in ("fused", "hide", "plain", "persistent", "resident"):
-            raise ValueError("mode must be fused | hide | plain | persistent | resident")
+        if mode not in ("fused", "hide", "plain", "persistent", "resident", "temporal"):
+            raise ValueError("mode must be fused | hide | plain | persistent | resident | temporal")
+        if mode == "temporal" and variant != "tma":
+            raise ValueError("mode='temporal' is a TMA kernel (variant='tma', even ny)")
         native.require()
         self.g = g
         self.nx, self.ny = nx, ny
@@ -60,7 +65,7 @@ class Diffusion2D:
         self.b_width = (int(b_width[0]), int(b_width[1]))
         dev = g.device
         self.transport = transport or default_transport(torch.empty(0, device=dev))
-        self.uses_peer = mode in ("fused", "hide", "persistent", "resident") or self.transport == "peer"
+        self.uses_peer = mode in ("fused", "hide", "persistent", "resident", "temporal") or self.transport == "peer"
         if mode in ("persistent", "resident"):
             variant = self.variant = "direct"      # the multi-step kernel reads the field through L2 directly
         if variant == "tma" and ny % 2:
@@ -76,8 +81,9 @@ class Diffusion2D:
         self._init_condition(host_ic)
         self.T2.copy_(self.T)                      # reference scripts/diffusion_2D_perf.jl:36
         self.plan: Optional[PushPlan] = None
-        if mode in ("fused", "hide", "persistent", "resident"):
+        if mode in ("fused", "hide", "persistent", "resident", "temporal"):
             self.plan = PushPlan(self.T, self.T2)
+        self._mid = self.plan.mid_lines() if (mode == "temporal" and self.plan.fab.neighbors) else None
         self._rflags = None
         self._repoch = 0
         if mode == "resident":
@@ -179,6 +185,24 @@ class Diffusion2D:
             if n % 2:
                 self.T, self.T2 = self.T2, self.T
             self.steps_done += n
+            return
+        if self.mode == "temporal":
+            if diag_out is not None:
+                raise ValueError("mode='temporal' has no in-kernel diagnostic")
+            ph = (self.lam, self.dt, self._dx, self._dy)
+            while n >= 2:
+                push = self.plan.next(self.T2, two_step=True)     # ONE epoch per pass of two steps
+                if push is not None:
+                    native.diffusion2d_midlines(self.T, self.Cp, *ph, push=push, mid=self._mid, dev_params=dev_params)
+                native.diffusion2d_step2(self.T2, self.T, self.Cp, *ph, push=push,
+                                         mid=self._mid if push is not None else None, dev_params=dev_params)
+                self.T, self.T2 = self.T2, self.T
+                self.steps_done += 2
+                n -= 2
+            if n == 1:
+                self._kernel(0, self.plan.next(self.T2), dev_params)
+                self.T, self.T2 = self.T2, self.T
+                self.steps_done += 1
             return
         if self.mode == "persistent":
             if dev_params is not None:

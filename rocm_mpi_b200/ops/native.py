@@ -20,6 +20,7 @@ _load_error: Optional[str] = None
 ERR_INVALID, ERR_UNSUPPORTED, ERR_TIMEOUT = -1, -2, -3
 FLAG_BANKS, BANK_STRIDE = 32, 64
 SLOT_DATA, SLOT_READY, SLOT_ERR, SLOT_CTA_COUNT = 0, 27, 54, 55
+SLOT_MID = 56                  # mid flags (flag pad) / mid CTA counters (counter pad) of sides 0..3
 MAX_HALO_FIELDS = 8
 
 
@@ -31,6 +32,12 @@ class Push2D(C.Structure):
 class Push3D(C.Structure):
     _fields_ = [("peer_dst", C.c_void_p * 27), ("peer_flag", C.c_void_p * 27), ("my_flag", C.c_void_p * 27),
                 ("my_count", C.c_void_p * 27), ("err_word", C.c_void_p), ("epoch", C.c_uint64)]
+
+
+class Mid2D(C.Structure):
+    """``igg_mid2d``: mid-line buffers and flags of the two-steps-per-pass kernel (sides: x-low, x-high, y-low, y-high)."""
+    _fields_ = [("my_mid", C.c_void_p), ("peer_mid", C.c_void_p * 4), ("peer_flag", C.c_void_p * 4),
+                ("my_flag", C.c_void_p * 4), ("my_count", C.c_void_p * 4)]
 
 
 class StepOpts(C.Structure):
@@ -95,6 +102,11 @@ def _declare(lib) -> None:
         "igg_colormap": ([vp, sz, d, d, vp, vp, vp], i),
         "igg_cpu_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d], i),
         "igg_cpu_diffusion2d_run": ([vp, vp, vp, i, i, d, d, d, d, i], i),
+        "igg_diffusion2d_step2": ([vp, vp, vp, i, i, d, d, d, d, vp, C.POINTER(Push2D), C.POINTER(Mid2D), vp], i),
+        "igg_diffusion2d_midlines": ([vp, vp, i, i, d, d, d, d, vp, C.POINTER(Push2D), C.POINTER(Mid2D), vp], i),
+        "igg_temporal2d_default_rows": ([], i),
+        "igg_cpu_temporal2d_emulate": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, vp, i], i),
+        "igg_cpu_temporal2d_midlines": ([vp, vp, i, i, d, d, d, d, C.POINTER(vp)], i),
     }
     for name, (argtypes, restype) in sig.items():
         fn = getattr(lib, name)
@@ -195,6 +207,32 @@ def diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: f
                                     C.byref(opts) if opts is not None else None,
                                     mode, int(b_width[0]), int(b_width[1]), VARIANTS[variant],
                                     C.byref(push) if push is not None else None, _stream()))
+
+
+def diffusion2d_step2(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
+                      _dy: float, push: Optional[Push2D] = None, mid: Optional["Mid2D"] = None,
+                      dev_params: Optional[torch.Tensor] = None) -> None:
+    """``T2 <- step(step(T))`` in one pass over memory (``igg_diffusion2d_step2``).  With neighbours, call
+    :func:`diffusion2d_midlines` with the same descriptors first (see ``parallel/fabric.py:PushPlan2``).
+    Experimental: validated through the host emulator only (:func:`cpu_temporal2d_emulate`)."""
+    lib = require()
+    nx, ny = T.shape
+    if T2.shape != T.shape or Cp.shape != T.shape:
+        raise ValueError("T, T2 and Cp must have the same shape")
+    _check(lib.igg_diffusion2d_step2(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
+                                     _f64(dev_params, "dev_params") if dev_params is not None else None,
+                                     C.byref(push) if push is not None else None,
+                                     C.byref(mid) if mid is not None else None, _stream()))
+
+
+def diffusion2d_midlines(T: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float, _dy: float,
+                         push: Push2D, mid: "Mid2D", dev_params: Optional[torch.Tensor] = None) -> None:
+    """Send this rank's step-(k+1) edge lines to the neighbours (``igg_diffusion2d_midlines``)."""
+    lib = require()
+    nx, ny = T.shape
+    _check(lib.igg_diffusion2d_midlines(_f64(T, "T"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
+                                        _f64(dev_params, "dev_params") if dev_params is not None else None,
+                                        C.byref(push), C.byref(mid), _stream()))
 
 
 def diffusion2d_step_controlled(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, params_pin: torch.Tensor,
@@ -382,6 +420,37 @@ def cpu_diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, la
             raise TypeError("cpu_diffusion2d_step needs contiguous CPU float64 tensors")
     nx, ny = T.shape
     _check(lib.igg_cpu_diffusion2d_step(T.data_ptr(), T2.data_ptr(), Cp.data_ptr(), nx, ny, lam, dt, _dx, _dy))
+
+
+def temporal2d_default_rows() -> int:
+    return int(require().igg_temporal2d_default_rows())
+
+
+def cpu_temporal2d_emulate(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam, dt, _dx, _dy, scx: int = 252,
+                           rpt: int = 2, workers: int = 148, mid_lines: Optional[torch.Tensor] = None,
+                           side_mask: int = 0) -> None:
+    """Run the index code of the two-steps-per-pass CUDA kernel on the host, thread by thread
+    (``igg_cpu_temporal2d_emulate``): ``T2 <- step(step(T))`` on the cells that kernel writes."""
+    lib = require()
+    for t in (T2, T, Cp) + ((mid_lines,) if mid_lines is not None else ()):
+        if t.is_cuda or t.dtype != torch.float64 or not t.is_contiguous():
+            raise TypeError("cpu_temporal2d_emulate needs contiguous CPU float64 tensors")
+    nx, ny = T.shape
+    if mid_lines is not None and mid_lines.numel() < 2 * nx + 2 * ny:
+        raise ValueError("mid_lines needs 2*nx + 2*ny elements")
+    _check(lib.igg_cpu_temporal2d_emulate(T.data_ptr(), T2.data_ptr(), Cp.data_ptr(), nx, ny, lam, dt, _dx, _dy,
+                                          scx, rpt, workers,
+                                          mid_lines.data_ptr() if mid_lines is not None else None, side_mask))
+
+
+def cpu_temporal2d_midlines(T: torch.Tensor, Cp: torch.Tensor, lam, dt, _dx, _dy,
+                            peer_mid: Sequence[Optional[torch.Tensor]]) -> None:
+    """Host version of ``igg_diffusion2d_midlines``: ``peer_mid[s]`` is the mid-line buffer of the neighbour on
+    side ``s`` (x-low, x-high, y-low, y-high) or ``None``."""
+    lib = require()
+    nx, ny = T.shape
+    arr = (C.c_void_p * 4)(*[(m.data_ptr() if m is not None else None) for m in peer_mid])
+    _check(lib.igg_cpu_temporal2d_midlines(T.data_ptr(), Cp.data_ptr(), nx, ny, lam, dt, _dx, _dy, arr))
 
 
 def cpu_diffusion2d_run(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam, dt, _dx, _dy, nt: int) -> None:

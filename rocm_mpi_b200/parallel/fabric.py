@@ -344,8 +344,38 @@ class PushPlan:
         for A in fields:
             self._desc[A.data_ptr()] = self._build(A)
         self._active = False
+        self._mid: Optional[native.Mid2D] = None
 
-    def _build(self, A: torch.Tensor):
+    def mid_lines(self) -> "native.Mid2D":
+        """Collective on first use: the mid-line buffers and flags of the two-steps-per-pass kernel
+        (``igg_diffusion2d_midlines`` / ``igg_diffusion2d_step2``; sides x-low, x-high, y-low, y-high)."""
+        if self._mid is None:
+            if self.ndim != 2:
+                raise ValueError("mid lines exist for 2-D fields only")
+            fab, bank = self.fab, self.bank
+            nx, ny = self.fields[0].shape
+            buf = fab.zeros((2 * nx + 2 * ny,))          # [xlo | xhi | ylo | yhi]
+            self._mid_buf = buf
+            m = native.Mid2D()
+            m.my_mid = buf.data_ptr()
+            ranks = dict(fab.neighbors)
+            for s, o in enumerate([(-1, 0, 0), (1, 0, 0), (0, -1, 0), (0, 1, 0)]):
+                r = ranks.get(o)
+                if r is None:
+                    continue
+                m.peer_mid[s] = fab.peer_ptr(buf, r)
+                # the neighbour on side s sees this rank on its opposite side (s ^ 1)
+                m.peer_flag[s] = fab.bank_ptr(bank, r) + (native.SLOT_MID + (s ^ 1)) * 8
+                m.my_flag[s] = fab.bank_ptr(bank) + (native.SLOT_MID + s) * 8
+                m.my_count[s] = fab.count_bank_ptr(bank) + (native.SLOT_MID + s) * 8
+            self._mid = m
+            # Arrival counters are compared modulo the number of edge tiles of the kernel that bumps them, and
+            # the two-step kernel tiles the field differently from the one-step kernel: it gets its own
+            # counters (counter-pad slots SLOT_READY.., unused otherwise) so the two can alternate.
+            self._desc2 = {A.data_ptr(): self._build(A, count_base=native.SLOT_READY) for A in self.fields}
+        return self._mid
+
+    def _build(self, A: torch.Tensor, count_base: int = 0):
         fab, bank = self.fab, self.bank
         my_bank, cnt_bank = fab.bank_ptr(bank), fab.count_bank_ptr(bank)
         d = native.Push2D() if self.ndim == 2 else native.Push3D()
@@ -355,7 +385,7 @@ class PushPlan:
             d.peer_dst[k] = fab.peer_ptr(A, r)
             d.peer_flag[k] = fab.bank_ptr(bank, r) + (native.SLOT_DATA + (26 - k3)) * 8
             d.my_flag[k] = my_bank + (native.SLOT_DATA + k3) * 8
-            d.my_count[k] = cnt_bank + k3 * 8
+            d.my_count[k] = cnt_bank + (count_base + k3) * 8
         d.err_word = my_bank + native.SLOT_ERR * 8
         d.epoch = 0
         return d
@@ -374,14 +404,14 @@ class PushPlan:
             native._check(self.fab.lib.igg_neighbor_barrier(C.byref(sync), native._stream()))
         self._active = True
 
-    def next(self, dst: torch.Tensor):
-        """Descriptor for the next step, whose results are written to ``dst`` (and its peers)."""
+    def next(self, dst: torch.Tensor, two_step: bool = False):
+        """Descriptor for the next step (or two-step pass), whose results are written to ``dst`` (and its peers)."""
         if not self._active:
             raise RuntimeError("PushPlan.begin() must be called before the time loop")
         if not self.fab.neighbors:
             return None
         self.epoch += 1
-        d = self._desc[dst.data_ptr()]
+        d = (self._desc2 if two_step else self._desc)[dst.data_ptr()]
         d.epoch = self.epoch
         return d
 

@@ -1,0 +1,126 @@
+"""The two-steps-per-pass kernel, checked without a GPU.
+
+``csrc/temporal2d_core.h`` holds the kernel's index code (work items, ring slots, the per-thread row loops
+of step 1 and step 2, masks, mid-line lookup); ``csrc/temporal2d_host.cpp`` compiles that same header for the
+CPU and runs it thread by thread.  These tests compare it bit for bit with two plain steps, on one rank and
+on virtual multi-rank grids where the halo width stays 1 and the neighbours' step-(k+1) edge lines travel
+half way (the reference only ever does one step per pass: ``scripts/diffusion_2D_perf.jl:47-52``).
+"""
+import pytest
+import torch
+
+from rocm_mpi_b200.ops import native
+from rocm_mpi_b200.ops import reference as ref
+from rocm_mpi_b200.parallel.topology import PROC_NULL
+from rocm_mpi_b200.parallel.virtual import VirtualGrid
+
+pytestmark = pytest.mark.skipif(not native.loaded(), reason="native library not built")
+
+PH = (1.3, 1e-3, 2.0, 3.0)   # lam, dt, 1/dx, 1/dy
+
+
+def _fields(nx, ny, seed=1):
+    g = torch.Generator().manual_seed(seed)
+    T = torch.rand(nx, ny, generator=g, dtype=torch.float64)
+    Cp = torch.rand(nx, ny, generator=g, dtype=torch.float64) + 0.5
+    return T, Cp
+
+
+def _two_steps(T, Cp):
+    a = T.clone()
+    ref.perf_step(a, T, Cp, *PH)
+    b = a.clone()
+    ref.perf_step(b, a, Cp, *PH)
+    return b
+
+
+@pytest.mark.parametrize("shape", [(3, 4), (4, 4), (5, 6), (17, 130), (40, 126), (41, 128), (64, 250),
+                                   (130, 258), (300, 380)])
+@pytest.mark.parametrize("rpt", [2, 4])
+def test_emulated_kernel_equals_two_steps(shape, rpt):
+    T, Cp = _fields(*shape)
+    want = _two_steps(T, Cp)
+    for scx, workers in [(12, 1), (12, 5), (28, 3), (252, 148)]:
+        T2 = T.clone()
+        native.cpu_temporal2d_emulate(T2, T, Cp, *PH, scx=scx, rpt=rpt, workers=workers)
+        assert torch.equal(T2, want), (shape, rpt, scx, workers, float((T2 - want).abs().max()))
+
+
+def test_boundary_cells_are_never_written():
+    T, Cp = _fields(70, 260)
+    T2 = torch.full_like(T, -7.0)
+    native.cpu_temporal2d_emulate(T2, T, Cp, *PH, scx=28, rpt=2, workers=4)
+    assert bool((T2[0] == -7).all() and (T2[-1] == -7).all() and (T2[:, 0] == -7).all() and (T2[:, -1] == -7).all())
+    assert bool((T2[1:-1, 1:-1] != -7).all())
+
+
+def test_rejects_bad_arguments():
+    T, Cp = _fields(20, 20)
+    with pytest.raises(native.NativeError):
+        native.cpu_temporal2d_emulate(T.clone(), T, Cp, *PH, scx=13)          # (scx + 4) % 16 != 0
+    with pytest.raises(native.NativeError):
+        native.cpu_temporal2d_emulate(T.clone(), T, Cp, *PH, rpt=3)
+    To, Co = _fields(20, 21)
+    with pytest.raises(native.NativeError):
+        native.cpu_temporal2d_emulate(To.clone(), To, Co, *PH)                # odd ny
+
+
+def _side_neighbors(vg, r):
+    """Rank on side s (x-low, x-high, y-low, y-high) of rank r, or PROC_NULL."""
+    nb = vg.topos[r].neighbors
+    return [nb[0][0], nb[1][0], nb[0][1], nb[1][1]]
+
+
+@pytest.mark.parametrize("dims,periods", [((2, 1), (0, 0)), ((1, 2), (0, 0)), ((2, 2), (0, 0)), ((3, 2), (0, 0)),
+                                          ((2, 2), (1, 1)), ((1, 1), (1, 1)), ((3, 1), (1, 0))])
+@pytest.mark.parametrize("local", [(20, 24), (37, 130)])
+def test_virtual_ranks_with_mid_lines(dims, periods, local):
+    _run_virtual(dims, periods, local, scx=12, rpt=2, workers=3)
+
+
+def _run_virtual(dims, periods, local, scx, rpt, workers):
+    """Per pass: every rank sends its step-(k+1) edge lines, runs the two-step pass, then the step-(k+2) halo
+    exchange happens (the in-kernel push of the real kernel).  Result == two (step + update_halo) rounds."""
+    nx, ny = local
+    vg = VirtualGrid((nx, ny), dims, periods)
+    n = vg.nprocs
+    gen = torch.Generator().manual_seed(5)
+    T = [torch.rand(nx, ny, dtype=torch.float64, generator=gen) for _ in range(n)]
+    Cp = [torch.rand(nx, ny, dtype=torch.float64, generator=gen) + 0.5 for _ in range(n)]
+    vg.update_halo(T)
+    vg.update_halo(Cp)
+
+    # reference: one step + halo update at a time
+    A = [t.clone() for t in T]
+    for _ in range(4):
+        B = [a.clone() for a in A]
+        for r in range(n):
+            ref.perf_step(B[r], A[r], Cp[r], *PH)
+        vg.update_halo(B)
+        A = B
+
+    # two passes of two steps
+    cur = [t.clone() for t in T]
+    mids = [torch.full((2 * nx + 2 * ny,), float("nan"), dtype=torch.float64) for _ in range(n)]
+    for _ in range(2):
+        for r in range(n):
+            sides = _side_neighbors(vg, r)
+            native.cpu_temporal2d_midlines(cur[r], Cp[r], *PH,
+                                           peer_mid=[mids[s] if s != PROC_NULL else None for s in sides])
+        nxt = [c.clone() for c in cur]
+        for r in range(n):
+            sides = _side_neighbors(vg, r)
+            mask = sum(1 << k for k, s in enumerate(sides) if s != PROC_NULL)
+            native.cpu_temporal2d_emulate(nxt[r], cur[r], Cp[r], *PH, scx=scx, rpt=rpt, workers=workers,
+                                          mid_lines=mids[r], side_mask=mask)
+        vg.update_halo(nxt)
+        cur = nxt
+    for r in range(n):
+        assert torch.equal(cur[r], A[r]), (r, float((cur[r] - A[r]).abs().max()))
+
+
+@pytest.mark.parametrize("dims,periods", [((1, 1), (1, 1)), ((2, 2), (0, 0)), ((2, 1), (1, 0))])
+def test_frame_first_item_order(dims, periods):
+    """With neighbours the items on the array edge come first (they push); needs >= 3 strips and >= 3 tile
+    columns to differ from row-major order.  Any item visited twice or not at all breaks the equality."""
+    _run_virtual(dims, periods, (44, 380), scx=12, rpt=4, workers=5)
