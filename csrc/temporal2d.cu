@@ -32,7 +32,7 @@ namespace {
 using namespace igg;
 using namespace igg_t2;
 
-constexpr int T2_SMEM_BYTES = (SNT + SNC + SNM) * BLK_BYTES + 256;
+constexpr int T2_SMEM_BYTES = RING_PAD * 8 + RING_DOUBLES * 8 + RING_PAD * 8 + 128;   // pad | rings | pad | mbarriers
 
 struct T2Params {
     double* T2;
@@ -61,10 +61,10 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
     constexpr int CONSUMERS = NPAIR * (SRB / RPT);
     constexpr int NCW = CONSUMERS / 32;
     extern __shared__ __align__(128) unsigned char smem[];
-    double* ringT = reinterpret_cast<double*>(smem);
+    double* ringT = reinterpret_cast<double*>(smem) + RING_PAD;      // 128 B in: still 128-byte aligned for TMA
     double* ringC = ringT + SNT * BLK;
     double* ringM = ringC + SNC * BLK;
-    uint64_t* fullT = reinterpret_cast<uint64_t*>(ringM + SNM * BLK);
+    uint64_t* fullT = reinterpret_cast<uint64_t*>(ringM + SNM * BLK + RING_PAD);
     uint64_t* emptyT = fullT + SNT;
     uint64_t* fullC = emptyT + SNT;
     uint64_t* emptyC = fullC + SNC;

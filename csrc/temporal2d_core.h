@@ -44,6 +44,11 @@ constexpr int SNC = 3;             // Cp ring: b-1, b in use + one in flight
 constexpr int SNM = 3;             // mid ring: b-1, b in use + the one step 1 of b+1 writes
 constexpr int BLK = SRB * BW;      // doubles per block
 constexpr int BLK_BYTES = BLK * 8; // 16384
+// The rings sit back to back (T, Cp, mid) with RING_PAD doubles of slack before the first and after the last
+// block: the left/right neighbour loads of box columns 0 and BW-1 are unconditional and may touch one element
+// outside a block.
+constexpr int RING_PAD = 16;
+constexpr int RING_DOUBLES = (SNT + SNC + SNM) * BLK;
 
 #if defined(__CUDACC__)
 typedef double2 d2;
@@ -185,8 +190,8 @@ T2_HD void step1_rows(const double* prevT, const double* curT, const double* nex
         const double* rc = curT + l * BW;
         const double* rn = (l + 1 < SRB) ? rc + BW : nextT;
         const d2 c = ld2(rn + col);
-        const double bl = cp > 0 ? rc[col - 1] : 0.0;
-        const double br = cp < NPAIR - 1 ? rc[col + 2] : 0.0;
+        const double bl = rc[col - 1];     // cp == 0 / NPAIR-1 read one element outside the row: in-bounds thanks
+        const double br = rc[col + 2];     // to RING_PAD, and only garbage columns 0 / BW-1 depend on it
         const d2 cc = ld2(curC + l * BW + col);
         const int x = xb + l;
         const bool vx = x >= 1 && x <= nx - 2;
@@ -228,8 +233,8 @@ T2_HD void step2_rows(const double* prevM, const double* curM, const double* pre
         const double* rn = curM + (lm + 1) * BW;                  // lm + 1 is in [0, SRB-1]
         const double* cr = lm >= 0 ? curC + lm * BW : prevC + (SRB + lm) * BW;
         const d2 c = ld2(rn + col);
-        const double bl = cp > 0 ? rc[col - 1] : 0.0;
-        const double br = cp < NPAIR - 1 ? rc[col + 2] : 0.0;
+        const double bl = rc[col - 1];
+        const double br = rc[col + 2];
         const d2 cc = ld2(cr + col);
         const int x = xb + lm;
         const bool vx = x >= x_lo && x <= x_hi;

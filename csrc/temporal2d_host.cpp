@@ -34,10 +34,13 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
     constexpr int NRG = SRB / RPT;
     const int nitems = num_items(g);
     // 16-byte aligned rings, poisoned so that a read of a slot that was never filled shows up
-    std::vector<d2> bufT(SNT * BLK / 2), bufC(SNC * BLK / 2), bufM(SNM * BLK / 2);
-    double* ringT = reinterpret_cast<double*>(bufT.data());
-    double* ringC = reinterpret_cast<double*>(bufC.data());
-    double* ringM = reinterpret_cast<double*>(bufM.data());
+    // same layout as the kernel's shared memory: pad | T ring | Cp ring | mid ring | pad
+    std::vector<d2> buf((RING_DOUBLES + 2 * RING_PAD) / 2);
+    double* base = reinterpret_cast<double*>(buf.data());
+    for (int i = 0; i < RING_DOUBLES + 2 * RING_PAD; ++i) base[i] = 1e300;
+    double* ringT = base + RING_PAD;
+    double* ringC = ringT + SNT * BLK;
+    double* ringM = ringC + SNC * BLK;
     for (int w = 0; w < workers; ++w) {
         for (int i = 0; i < SNT * BLK; ++i) ringT[i] = 1e300;
         for (int i = 0; i < SNC * BLK; ++i) ringC[i] = 1e300;
