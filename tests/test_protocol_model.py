@@ -145,3 +145,136 @@ def test_model_catches_a_broken_protocol():
     with pytest.raises(AssertionError):
         for seed in range(200):
             broken(3, seed)
+
+
+# ======================================================================================================
+# Two-steps-per-pass launches mixed with one-step launches (csrc/temporal2d.cu)
+# ======================================================================================================
+# A pass of epoch e is two kernels in stream order: F(e) ("mid lines": every CTA first waits for the DATA flags
+# e-1 of BOTH neighbours, then stores its part of the rank's step-(k+1) edge line into the neighbour's mid
+# buffer; the last CTA of a face releases the neighbour's mid flag e) and B(e) (edge items wait for the mid flag
+# e of their side, read the mid line and the halo, push the step-(k+2) edge into the neighbour's new buffer;
+# the last one releases DATA e).  B(e) itself never waits for DATA e-1: F(e) did, earlier on the same stream.
+# A one-step launch S(e) behaves as in the model above.  One epoch per launch, buffers alternate per launch.
+class Rank2:
+    def __init__(self, r, sched, nte, nti, nf):
+        self.r, self.nte, self.nti, self.nf = r, nte, nti, nf
+        self.kernels = []
+        for e, s in enumerate(sched, start=1):
+            self.kernels += [("S", e)] if s == "S" else [("F", e), ("B", e)]
+        self.k = 0
+        self.halo = [[0, 0], [0, 0]]
+        self.mid = [0, 0]
+        self.data_flag = [0, 0]
+        self.mid_flag = [0, 0]
+        self.cnt = {"S": [0, 0], "B": [0, 0], "F": [0, 0]}     # the kernels keep separate arrival counters
+        self.todo = self._tiles()
+
+    def _tiles(self):
+        if self.k >= len(self.kernels):
+            return []
+        kind, _ = self.kernels[self.k]
+        if kind == "F":
+            return [("face", s, "wait") for s in (0, 1) for _ in range(self.nf)]
+        return [("edge", s, "wait") for s in (0, 1) for _ in range(self.nte)] + [("interior", None, "run")] * self.nti
+
+    def done(self):
+        return self.k >= len(self.kernels)
+
+    def pending_readers(self, what, side, e):
+        """Does this rank still have to read `what` ('mid' or the halo of buffer e % 2) on `side` in a launch
+        older than e?"""
+        for idx in range(self.k, len(self.kernels)):
+            kind, ee = self.kernels[idx]
+            if ee >= e:
+                break
+            todo = self.todo if idx == self.k else None          # None = not started: everything pending
+            if what == "mid":
+                if kind == "F":
+                    return True                                  # its B(ee) comes later and reads the mid line
+                if kind == "B" and (todo is None or any(t == ("edge", side, "wait") for t in todo)):
+                    return True
+            else:
+                if (ee - 1) % 2 != e % 2:
+                    continue                                     # that launch reads the other buffer
+                if kind == "F":
+                    if todo is None or any(t[0] == "face" and t[2] == "wait" for t in todo):
+                        return True                              # F CTAs read the halos of both sides
+                elif todo is None or any(t == ("edge", side, "wait") for t in todo):
+                    return True
+        return False
+
+
+def simulate_mixed(nranks, sched, nte, nti, nf, seed, weaken=None):
+    rng = random.Random(seed)
+    ranks = [Rank2(r, sched, nte, nti, nf) for r in range(nranks)]
+    while not all(rk.done() for rk in ranks):
+        cand = []
+        for rk in ranks:
+            if rk.done():
+                continue
+            kind, e = rk.kernels[rk.k]
+            for i, (tk, side, phase) in enumerate(rk.todo):
+                if phase == "wait":
+                    if kind == "S" and rk.data_flag[side] < e - 1:
+                        continue
+                    if kind == "B" and rk.mid_flag[side] < (e - 1 if weaken == "mid" else e):
+                        continue
+                    if kind == "F" and weaken != "data" and min(rk.data_flag) < e - 1:
+                        continue
+                cand.append((rk, i))
+        assert cand, "deadlock: no enabled operation"
+        rk, i = rng.choice(cand)
+        kind, e = rk.kernels[rk.k]
+        tk, side, phase = rk.todo[i]
+        old_buf, new_buf = (e - 1) % 2, e % 2
+        if tk == "interior":
+            rk.todo.pop(i)
+        elif phase == "wait":
+            if kind == "F":
+                assert rk.halo[old_buf] == [e - 1, e - 1], f"RAW: F({e}) on rank {rk.r} read halos {rk.halo[old_buf]}"
+                rk.todo[i] = (tk, side, "store")
+            else:
+                assert rk.halo[old_buf][side] == e - 1, f"RAW: {kind}({e}) rank {rk.r} side {side} halo {rk.halo[old_buf][side]}"
+                if kind == "B":
+                    assert rk.mid[side] == e, f"RAW: B({e}) rank {rk.r} side {side} read mid version {rk.mid[side]}"
+                rk.todo[i] = (tk, side, "push")
+        else:
+            nb = ranks[(rk.r + (1 if side == 1 else -1)) % nranks]
+            nb_side = 1 - side
+            if phase == "store":
+                assert not nb.pending_readers("mid", nb_side, e), \
+                    f"WAR: F({e}) of rank {rk.r} overwrites a mid line rank {nb.r} has not read yet"
+                rk.cnt["F"][side] += 1
+                if rk.cnt["F"][side] % rk.nf == 0:
+                    assert nb.mid_flag[nb_side] < e
+                    nb.mid[nb_side] = e
+                    nb.mid_flag[nb_side] = e
+            else:
+                assert not nb.pending_readers("halo", nb_side, e), \
+                    f"WAR: {kind}({e}) of rank {rk.r} overwrites a halo rank {nb.r} has not read yet"
+                rk.cnt[kind][side] += 1
+                if rk.cnt[kind][side] % rk.nte == 0:
+                    assert nb.data_flag[nb_side] == e - 1, "epochs must be released in order"
+                    nb.halo[new_buf][nb_side] = e
+                    nb.data_flag[nb_side] = e
+            rk.todo.pop(i)
+        if not rk.todo:
+            rk.k += 1
+            rk.todo = rk._tiles()
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 5])
+@pytest.mark.parametrize("sched", ["PPPPPP", "PSPSPP", "SSPPSS", "PPPS", "SPSPSPS"])
+def test_two_step_passes_are_race_and_deadlock_free(nranks, sched):
+    for seed in range(25):
+        simulate_mixed(nranks, sched, nte=3, nti=3, nf=2, seed=seed)
+
+
+@pytest.mark.parametrize("weaken", ["mid", "data"])
+def test_mixed_model_catches_broken_waits(weaken):
+    """The checker must notice a B that accepts the previous pass's mid flag, and an F that does not wait for
+    the neighbours' DATA flags."""
+    with pytest.raises(AssertionError):
+        for seed in range(300):
+            simulate_mixed(3, "PPPPPP", nte=2, nti=1, nf=2, seed=seed, weaken=weaken)
