@@ -23,11 +23,22 @@ from ..utils.config import DiffusionConfig, add_config_args, config_from_args
 from ..utils.profiling import nvtx_range
 from .common import detach_local, RunResult, log0, setup_2d, visualise_2d
 from .solver import Diffusion2D
+from .solver_host import Diffusion2DHost
 
-__all__ = ["diffusion2D_perf", "run_timed", "main"]
+__all__ = ["diffusion2D_perf", "run_timed", "make_solver", "main"]
 
 
-def run_timed(s: Diffusion2D, nt: int, warmup: int) -> float:
+def make_solver(cfg: DiffusionConfig, mode: str):
+    """The GPU stepper, or its CPU stand-in when the grid lives on the host (``--device-type cpu``): there a
+    ``fused`` request degrades to the serial structure, ``hide`` keeps its frame / exchange / interior order."""
+    if global_grid().device_type != "cuda":
+        return Diffusion2DHost(cfg.nx, cfg.ny, lx=cfg.lx, ly=cfg.ly, lam=cfg.lam, Cp0=cfg.Cp0,
+                               mode="hide" if mode == "hide" else "plain", b_width=cfg.b_width[:2])
+    return Diffusion2D(cfg.nx, cfg.ny, lx=cfg.lx, ly=cfg.ly, lam=cfg.lam, Cp0=cfg.Cp0, mode=mode, variant=cfg.kernel,
+                       b_width=cfg.b_width[:2], transport=cfg.transport)
+
+
+def run_timed(s, nt: int, warmup: int) -> float:
     """The reference's time loop: ``tic()`` once ``warmup`` iterations are done, ``toc()`` at the end."""
     s.begin()
     gc_was = gc.isenabled()
@@ -50,14 +61,10 @@ def diffusion2D_perf(cfg: DiffusionConfig = None, mode: str = None, variant_name
                      finalize: bool = True) -> RunResult:
     cfg = cfg or DiffusionConfig(nx=16384, ny=16384, nt=110, do_vis=False)
     su = setup_2d(cfg)
-    g = global_grid()
-    if g.device_type != "cuda":
-        raise RuntimeError("diffusion2D_perf needs a CUDA device (use diffusion2d_ap for the CPU path)")
     if mode is None:
         mode = "fused" if cfg.fused else "plain"
     n0 = native.launch_count()
-    s = Diffusion2D(cfg.nx, cfg.ny, lx=cfg.lx, ly=cfg.ly, lam=cfg.lam, Cp0=cfg.Cp0, mode=mode, variant=cfg.kernel,
-                    b_width=cfg.b_width[:2], transport=cfg.transport)
+    s = make_solver(cfg, mode)
     nt, warm = int(cfg.nt), min(int(cfg.warmup), max(int(cfg.nt) - 1, 0))
     log0("Starting the time loop ...", end="")
     wtime = run_timed(s, nt, warm)

@@ -19,8 +19,7 @@ from ..parallel import a_eff, finalize_global_grid, global_grid
 from ..utils.config import DiffusionConfig, add_config_args, config_from_args
 from ..utils.profiling import HostProfile, cuda_profiler_range
 from .common import detach_local, RunResult, log0, setup_2d
-from .diffusion2d_perf import run_timed
-from .solver import Diffusion2D
+from .diffusion2d_perf import make_solver, run_timed
 
 __all__ = ["diffusion2D_perf_hide_prof", "main"]
 
@@ -33,9 +32,7 @@ def diffusion2D_perf_hide_prof(cfg: DiffusionConfig = None, prof_path: str = "pr
     su = setup_2d(cfg)
     g = global_grid()
     n0 = native.launch_count()
-    s = Diffusion2D(cfg.nx, cfg.ny, lx=cfg.lx, ly=cfg.ly, lam=cfg.lam, Cp0=cfg.Cp0,
-                    mode="fused" if cfg.fused else "hide", variant=cfg.kernel, b_width=cfg.b_width[:2],
-                    transport=cfg.transport)
+    s = make_solver(cfg, "fused" if cfg.fused else "hide")
     nt, warm = int(cfg.nt), min(int(cfg.warmup), max(int(cfg.nt) - 1, 0))
     hp = HostProfile()
     with hp:

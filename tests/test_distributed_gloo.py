@@ -39,6 +39,13 @@ def test_kp_3d_and_hide_communication_over_gloo(nprocs, tmp_path):
     assert all("ok" in o for o in outs)
 
 
+@pytest.mark.parametrize("nprocs", [4, 8])
+def test_perf_apps_on_cpu_over_gloo(nprocs, tmp_path):
+    """perf / perf_hide / perf_hide_prof through their CPU stand-in stepper (models/solver_host.py)."""
+    outs = run_workers("perf_gloo.py", nprocs, (str(tmp_path), nprocs), timeout=600)
+    assert all("ok" in o for o in outs)
+
+
 def test_ring_smoke_test_over_gloo():
     outs = run_workers("ring_gloo.py", 4)
     assert all("ok" in o for o in outs)
