@@ -25,6 +25,11 @@ reference's ``IGG_ROCMAWARE_MPI`` switch, ``scripts/setenv.sh:11-18``):
           ``IGG_ROCMAWARE_MPI=0`` analogue, reference ``README.md:25-35``)
 ``gloo``  CPU tensors (plumbing / tests)
 ========  ==============================================================================
+
+Upstream ImplicitGlobalGrid also has per-dimension switches (``IGG_ROCMAWARE_MPI_DIMX/_DIMY/_DIMZ``, SURVEY.md
+G9).  Their analogue: ``IGG_B200_TRANSPORT_DIMX`` / ``_DIMY`` / ``_DIMZ`` = ``nccl`` or ``host`` choose, per
+dimension, between device-direct messages and pinned-host staging inside the pack/exchange/unpack engine
+(transports ``nccl`` and ``host``; the one-launch ``peer`` engine has no per-dimension stages to switch).
 """
 from __future__ import annotations
 
@@ -37,7 +42,8 @@ import torch
 from .grid import GlobalGrid, global_grid
 from .topology import NDIMS, PROC_NULL
 
-__all__ = ["update_halo", "halo_planes", "halo_boxes", "HaloSpec", "default_transport", "ExchangeHalo"]
+__all__ = ["update_halo", "halo_planes", "halo_boxes", "HaloSpec", "default_transport", "ExchangeHalo",
+           "per_dim_staging"]
 
 
 @dataclass(frozen=True)
@@ -116,6 +122,18 @@ def default_transport(field: torch.Tensor) -> str:
     return "peer"
 
 
+def per_dim_staging(transport: str) -> Tuple[bool, bool, bool]:
+    """Per dimension: are messages staged through pinned host memory?  (``transport`` is ``nccl`` or ``host``;
+    ``IGG_B200_TRANSPORT_DIMX/Y/Z`` override it for single dimensions.)"""
+    out = []
+    for d in "XYZ":
+        env = os.environ.get(f"IGG_B200_TRANSPORT_DIM{d}", "").strip().lower()
+        if env and env not in ("nccl", "host"):
+            raise ValueError(f"IGG_B200_TRANSPORT_DIM{d} must be nccl|host, got {env!r}")
+        out.append((env or transport) == "host")
+    return tuple(out)
+
+
 def _check_fields(g: GlobalGrid, fields: Sequence[torch.Tensor]) -> None:
     if not fields:
         raise ValueError("update_halo needs at least one field")
@@ -144,6 +162,7 @@ class ExchangeHalo:
         self.transport = transport
         self._bufs: Dict[tuple, torch.Tensor] = {}
         self.launches = 0  # native kernels launched (pack/unpack), for accounting
+        self.host_dims = per_dim_staging(transport) if transport in ("nccl", "host") else (False,) * NDIMS
 
     # -- buffers -----------------------------------------------------------------------
     def _buf(self, key: tuple, numel: int, like: torch.Tensor, pinned_host: bool = False) -> torch.Tensor:
@@ -180,8 +199,8 @@ class ExchangeHalo:
     def update(self, fields: Sequence[torch.Tensor]) -> None:
         g = self.g
         specs = [halo_planes(g.nxyz, g.overlaps, A.shape) for A in fields]
-        host = self.transport == "host"
         for dim in range(NDIMS):
+            host = self.host_dims[dim]
             sends, recvs, unpacks = [], [], []
             for f, A in enumerate(fields):
                 spec = specs[f][dim]

@@ -101,3 +101,19 @@ def test_wider_overlaps_box_form_and_global_size(overlaps):
     vg.update_halo_boxes(b)
     for r in range(vg.nprocs):
         assert torch.equal(a[r], b[r])
+
+
+def test_per_dimension_transport_switches(monkeypatch):
+    """IGG_B200_TRANSPORT_DIMX/Y/Z: the analogue of upstream's IGG_ROCMAWARE_MPI_DIMX/_DIMY/_DIMZ."""
+    from rocm_mpi_b200.parallel.halo import per_dim_staging
+    for d in "XYZ":
+        monkeypatch.delenv(f"IGG_B200_TRANSPORT_DIM{d}", raising=False)
+    assert per_dim_staging("nccl") == (False, False, False)
+    assert per_dim_staging("host") == (True, True, True)
+    monkeypatch.setenv("IGG_B200_TRANSPORT_DIMY", "host")
+    assert per_dim_staging("nccl") == (False, True, False)
+    monkeypatch.setenv("IGG_B200_TRANSPORT_DIMX", "nccl")
+    assert per_dim_staging("host") == (False, True, True)
+    monkeypatch.setenv("IGG_B200_TRANSPORT_DIMZ", "mpi")
+    with pytest.raises(ValueError):
+        per_dim_staging("nccl")
