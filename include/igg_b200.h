@@ -289,6 +289,15 @@ int igg_cpu_diffusion2d_step(const double* T, double* T2, const double* Cp, int 
                              double dt, double _dx, double _dy);
 int igg_cpu_diffusion2d_run(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
                             double _dx, double _dy, int nt);
+/* three-kernel form on the CPU (reference scripts/diffusion_2D_kp.jl:16-54); qx (nx-1)x(ny-2), qy (nx-2)x(ny-1),
+ * dTdt (nx-2)x(ny-2), row-major */
+int igg_cpu_flux2d(double* qx, double* qy, const double* T, int nx, int ny, double lam, double _dx, double _dy);
+int igg_cpu_residual2d(double* dTdt, const double* qx, const double* qy, const double* Cp, int nx, int ny,
+                       double _dx, double _dy);
+int igg_cpu_update2d(double* T, const double* dTdt, int nx, int ny, double dt);
+/* 3-D fused step on the CPU (what igg_diffusion3d_step computes in mode 0) */
+int igg_cpu_diffusion3d_step(const double* T, double* T2, const double* Cp, int nx, int ny, int nz, double lam,
+                             double dt, double _dx, double _dy, double _dz);
 
 #ifdef __cplusplus
 }

@@ -58,6 +58,7 @@ def diffusion2D_kp(cfg: DiffusionConfig = None, finalize: bool = True) -> RunRes
     else:
         T = T0
     n0 = native.launch_count()
+    cpu_native = (not on_gpu) and native.loaded() and T.is_contiguous()
 
     plan = None
     if fused_push:
@@ -87,7 +88,10 @@ def diffusion2D_kp(cfg: DiffusionConfig = None, finalize: bool = True) -> RunRes
                 if comm_needed:
                     update_halo(T, transport=transport)
         else:
-            ref.kp_step(T, Cp, qx, qy, dTdt, cfg.lam, s.dt, _dx, _dy)
+            if cpu_native:                 # the three kernels as OpenMP loop nests (csrc/cpu_oracle.cpp)
+                native.cpu_kp_step(T, Cp, qx, qy, dTdt, cfg.lam, s.dt, _dx, _dy)
+            else:
+                ref.kp_step(T, Cp, qx, qy, dTdt, cfg.lam, s.dt, _dx, _dy)
             if comm_needed:
                 update_halo(T)
     if plan is not None:

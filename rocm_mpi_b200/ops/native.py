@@ -102,6 +102,10 @@ def _declare(lib) -> None:
         "igg_colormap": ([vp, sz, d, d, vp, vp, vp], i),
         "igg_cpu_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d], i),
         "igg_cpu_diffusion2d_run": ([vp, vp, vp, i, i, d, d, d, d, i], i),
+        "igg_cpu_flux2d": ([vp, vp, vp, i, i, d, d, d], i),
+        "igg_cpu_residual2d": ([vp, vp, vp, vp, i, i, d, d], i),
+        "igg_cpu_update2d": ([vp, vp, i, i, d], i),
+        "igg_cpu_diffusion3d_step": ([vp, vp, vp, i, i, i, d, d, d, d, d], i),
         "igg_diffusion2d_step2": ([vp, vp, vp, i, i, d, d, d, d, vp, C.POINTER(Push2D), C.POINTER(Mid2D), vp], i),
         "igg_diffusion2d_midlines": ([vp, vp, i, i, d, d, d, d, vp, C.POINTER(Push2D), C.POINTER(Mid2D), vp], i),
         "igg_temporal2d_default_rows": ([], i),
@@ -420,6 +424,32 @@ def cpu_diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, la
             raise TypeError("cpu_diffusion2d_step needs contiguous CPU float64 tensors")
     nx, ny = T.shape
     _check(lib.igg_cpu_diffusion2d_step(T.data_ptr(), T2.data_ptr(), Cp.data_ptr(), nx, ny, lam, dt, _dx, _dy))
+
+
+def _cpu_f64(*ts: torch.Tensor) -> None:
+    for t in ts:
+        if t.is_cuda or t.dtype != torch.float64 or not t.is_contiguous():
+            raise TypeError("the CPU restatements need contiguous CPU float64 tensors")
+
+
+def cpu_kp_step(T: torch.Tensor, Cp: torch.Tensor, qx: torch.Tensor, qy: torch.Tensor, dTdt: torch.Tensor, lam, dt,
+                _dx, _dy) -> None:
+    """``Flux!``, ``Residual!``, ``Update!`` on the CPU (OpenMP), in place on ``T`` like ``ops.reference.kp_step``."""
+    lib = require()
+    _cpu_f64(T, Cp, qx, qy, dTdt)
+    nx, ny = T.shape
+    if tuple(qx.shape) != (nx - 1, ny - 2) or tuple(qy.shape) != (nx - 2, ny - 1) or tuple(dTdt.shape) != (nx - 2, ny - 2):
+        raise ValueError("qx, qy, dTdt must be (nx-1, ny-2), (nx-2, ny-1), (nx-2, ny-2)")
+    _check(lib.igg_cpu_flux2d(qx.data_ptr(), qy.data_ptr(), T.data_ptr(), nx, ny, lam, _dx, _dy))
+    _check(lib.igg_cpu_residual2d(dTdt.data_ptr(), qx.data_ptr(), qy.data_ptr(), Cp.data_ptr(), nx, ny, _dx, _dy))
+    _check(lib.igg_cpu_update2d(T.data_ptr(), dTdt.data_ptr(), nx, ny, dt))
+
+
+def cpu_diffusion3d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam, dt, _dx, _dy, _dz) -> None:
+    lib = require()
+    _cpu_f64(T2, T, Cp)
+    nx, ny, nz = T.shape
+    _check(lib.igg_cpu_diffusion3d_step(T.data_ptr(), T2.data_ptr(), Cp.data_ptr(), nx, ny, nz, lam, dt, _dx, _dy, _dz))
 
 
 def temporal2d_default_rows() -> int:

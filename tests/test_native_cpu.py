@@ -40,3 +40,31 @@ def test_cpu_run_matches_oracle():
     Cp = torch.ones_like(T)
     native.cpu_diffusion2d_run(T, T2, Cp, 1.0, dt, 1.0 / dx, 1.0 / dy, 25)
     assert torch.equal(T, T_ref)
+
+
+def test_cpu_kp_kernels_match_reference():
+    g = torch.Generator().manual_seed(11)
+    for (nx, ny) in [(3, 3), (9, 14), (37, 52)]:
+        T = torch.rand(nx, ny, generator=g, dtype=torch.float64)
+        Cp = torch.rand(nx, ny, generator=g, dtype=torch.float64) + 0.5
+        bufs = lambda: (torch.zeros(nx - 1, ny - 2, dtype=torch.float64), torch.zeros(nx - 2, ny - 1, dtype=torch.float64),
+                        torch.zeros(nx - 2, ny - 2, dtype=torch.float64))
+        want, got = T.clone(), T.clone()
+        qa, qb = bufs(), bufs()
+        for _ in range(3):
+            ref.kp_step(want, Cp, *qa, 1.3, 1e-3, 2.0, 3.0)
+            native.cpu_kp_step(got, Cp, *qb, 1.3, 1e-3, 2.0, 3.0)
+        assert torch.equal(got, want)
+        assert all(torch.equal(a, b) for a, b in zip(qa, qb))
+
+
+def test_cpu_3d_step_matches_reference():
+    g = torch.Generator().manual_seed(12)
+    for shape in [(3, 3, 3), (7, 9, 11), (20, 17, 18)]:
+        T = torch.rand(*shape, generator=g, dtype=torch.float64)
+        Cp = torch.rand(*shape, generator=g, dtype=torch.float64) + 0.5
+        want = T.clone()
+        ref.perf_step_3d(want, T, Cp, 1.1, 1e-3, 2.0, 3.0, 4.0)
+        got = T.clone()
+        native.cpu_diffusion3d_step(got, T, Cp, 1.1, 1e-3, 2.0, 3.0, 4.0)
+        assert torch.equal(got, want)
