@@ -30,8 +30,11 @@ __all__ = ["Diffusion3D", "diffusion3D", "main"]
 
 
 class Diffusion3D:
-    """3-D time stepper: ``fused`` (one launch per step, edges pushed in-kernel) or ``plain``
-    (kernel, swap, ``update_halo`` over a transport)."""
+    """3-D time stepper: ``fused`` (one launch per step, edges pushed in-kernel), ``plain`` (kernel, swap,
+    ``update_halo`` over a transport) or ``hide`` (the two-stream structure of reference
+    ``scripts/diffusion_2D_perf_hide.jl:63-68, 94-101`` carried to 3-D: boundary frame of width ``b_width`` +
+    edge push on a high-priority stream, interior on a low-priority stream, join, swap; its two kernels are
+    GPU-tested individually, the two-stream driver itself has not been run on hardware yet)."""
 
     def __init__(self, nx: int, ny: int, nz: int, *, lx=10.0, ly=10.0, lz=10.0, lam=1.0, Cp0=1.0,
                  mode: str = "fused", variant: str = "tma", b_width: Sequence[int] = (4, 4, 8),
@@ -41,8 +44,8 @@ class Diffusion3D:
             raise RuntimeError("Diffusion3D runs on CUDA devices")
         if (nx, ny, nz) != tuple(g.nxyz):
             raise ValueError("nx, ny, nz must be the local sizes given to init_global_grid")
-        if mode not in ("fused", "plain"):
-            raise ValueError("mode must be fused | plain")
+        if mode not in ("fused", "plain", "hide"):
+            raise ValueError("mode must be fused | plain | hide")
         if variant == "tma" and nz % 2:
             raise ValueError("variant 'tma' needs an even nz; use variant='direct'")
         native.require()
@@ -54,7 +57,7 @@ class Diffusion3D:
         self.mode, self.variant, self.b_width = mode, variant, tuple(int(b) for b in b_width)
         dev = g.device
         self.transport = transport or default_transport(torch.empty(0, device=dev))
-        peer = mode == "fused" or self.transport == "peer"
+        peer = mode in ("fused", "hide") or self.transport == "peer"
         mk = fabric_zeros if peer else (lambda s: torch.zeros(s, dtype=torch.float64, device=dev))
         self.T, self.T2 = mk(self.shape), mk(self.shape)
         self.Cp = torch.full(self.shape, float(Cp0), dtype=torch.float64, device=dev)
@@ -66,8 +69,13 @@ class Diffusion3D:
             o = [float(coords_g(d, h, probe)[0]) for d, h in enumerate((self.dx, self.dy, self.dz))]
             native.gaussian_ic_3d(self.T, o[0], o[1], o[2], self.dx, self.dy, self.dz, lx, ly, lz)
         self.T2.copy_(self.T)
-        self.plan = PushPlan(self.T, self.T2) if mode == "fused" else None
+        self.plan = PushPlan(self.T, self.T2) if mode in ("fused", "hide") else None
         self._running = False
+        self._s_hi = self._s_lo = None
+        if mode == "hide":
+            self._s_hi = torch.cuda.Stream(device=dev, priority=-1)
+            self._s_lo = torch.cuda.Stream(device=dev, priority=0)
+            self._ev_main, self._ev_hi, self._ev_lo = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
 
     def begin(self) -> None:
         if self.plan is not None:
@@ -77,17 +85,37 @@ class Diffusion3D:
         self._running = True
 
     def finish(self) -> None:
+        if self._s_hi is not None:
+            torch.cuda.current_stream().wait_stream(self._s_hi)
+            torch.cuda.current_stream().wait_stream(self._s_lo)
         if self.plan is not None and self._running:
             self.plan.finish()
         self._running = False
+
+    def _kernel(self, mode: int, push) -> None:
+        native.diffusion3d_step(self.T2, self.T, self.Cp, self.lam, self.dt, *self._d, mode=mode,
+                                b_width=self.b_width, variant=self.variant, push=push)
 
     def step(self, n: int = 1) -> None:
         if not self._running:
             self.begin()
         for _ in range(n):
             push = self.plan.next(self.T2) if self.plan is not None else None
-            native.diffusion3d_step(self.T2, self.T, self.Cp, self.lam, self.dt, *self._d, mode=0,
-                                    b_width=self.b_width, variant=self.variant, push=push)
+            if self.mode == "hide":
+                main = torch.cuda.current_stream()
+                self._ev_main.record(main)
+                self._s_hi.wait_event(self._ev_main)
+                self._s_lo.wait_event(self._ev_main)
+                with torch.cuda.stream(self._s_hi):
+                    self._kernel(1, push)                 # frame + edge push
+                    self._ev_hi.record(self._s_hi)
+                with torch.cuda.stream(self._s_lo):
+                    self._kernel(2, None)                 # interior
+                    self._ev_lo.record(self._s_lo)
+                main.wait_event(self._ev_hi)
+                main.wait_event(self._ev_lo)
+            else:
+                self._kernel(0, push)
             self.T, self.T2 = self.T2, self.T
             if self.plan is None and (self.g.nprocs > 1 or any(self.g.periods)):
                 update_halo(self.T, transport=self.transport)
