@@ -121,7 +121,7 @@ class Diffusion3D:
                 update_halo(self.T, transport=self.transport)
 
 
-def diffusion3D(cfg: DiffusionConfig = None, finalize: bool = True) -> RunResult:
+def diffusion3D(cfg: DiffusionConfig = None, finalize: bool = True, mode: Optional[str] = None) -> RunResult:
     cfg = cfg or DiffusionConfig(nx=256, ny=256, nz=256, nt=60, do_vis=False)
     me, dims, nprocs, coords, _ = init_global_grid(
         cfg.nx, cfg.ny, cfg.nz, dimx=cfg.dimx, dimy=cfg.dimy, dimz=cfg.dimz, periodx=cfg.periodx,
@@ -133,7 +133,7 @@ def diffusion3D(cfg: DiffusionConfig = None, finalize: bool = True) -> RunResult
         return _diffusion3D_cpu(cfg, me, dims, nprocs, finalize)
     n0 = native.launch_count()
     s = Diffusion3D(cfg.nx, cfg.ny, cfg.nz, lx=cfg.lx, ly=cfg.ly, lz=cfg.lz, lam=cfg.lam, Cp0=cfg.Cp0,
-                    mode="fused" if cfg.fused else "plain", variant=cfg.kernel, b_width=cfg.b_width,
+                    mode=mode or ("fused" if cfg.fused else "plain"), variant=cfg.kernel, b_width=cfg.b_width,
                     transport=cfg.transport)
     nt, warm = int(cfg.nt), min(int(cfg.warmup), max(int(cfg.nt) - 1, 0))
     log0("Starting the time loop ...", end="")
@@ -196,7 +196,10 @@ def _diffusion3D_cpu(cfg: DiffusionConfig, me: int, dims, nprocs: int, finalize:
 def main(argv=None) -> None:
     p = argparse.ArgumentParser(description=__doc__.split("\n")[0])
     add_config_args(p, DiffusionConfig(nx=256, ny=256, nz=256, nt=60, do_vis=False, b_width=(4, 4, 8)))
-    diffusion3D(config_from_args(p.parse_args(argv)))
+    p.add_argument("--mode", default=None, choices=["fused", "plain", "hide"],
+                   help="time-stepper structure (default: fused, or plain with --fused false)")
+    ns = p.parse_args(argv)
+    diffusion3D(config_from_args(ns), mode=ns.mode)
 
 
 if __name__ == "__main__":
