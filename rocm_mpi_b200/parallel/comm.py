@@ -20,7 +20,7 @@ from typing import Any, List, Optional, Sequence
 
 import torch
 
-__all__ = ["Comm", "SelfComm", "TorchComm", "local_rank", "launcher_env_present", "make_comm"]
+__all__ = ["Comm", "SelfComm", "TorchComm", "local_rank", "launcher_env_present", "make_comm", "spans_nodes"]
 
 
 def launcher_env_present() -> bool:
@@ -37,6 +37,18 @@ def local_rank() -> int:
         if key in os.environ:
             return int(os.environ[key])
     return 0
+
+
+def spans_nodes() -> bool:
+    """True when the job has more ranks than this node hosts (``torchrun`` exports ``LOCAL_WORLD_SIZE``).
+
+    The peer fabric maps memory with CUDA IPC, i.e. inside one NVSwitch domain; across nodes the halo exchange
+    has to use the NCCL transport (the reference's multi-node story is likewise the launcher's:
+    ``srun -n 4 --mpi=pmix``, ``README.md:16-18``)."""
+    try:
+        return int(os.environ.get("WORLD_SIZE", "1")) > int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
+    except ValueError:
+        return False
 
 
 class Comm:

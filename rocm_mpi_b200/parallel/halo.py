@@ -119,7 +119,8 @@ def default_transport(field: torch.Tensor) -> str:
         if env not in ("peer", "nccl", "host"):
             raise ValueError(f"IGG_B200_TRANSPORT must be peer|nccl|host, got {env!r}")
         return env
-    return "peer"
+    from .comm import spans_nodes
+    return "nccl" if spans_nodes() else "peer"      # CUDA IPC peer mappings end at the node boundary
 
 
 def per_dim_staging(transport: str) -> Tuple[bool, bool, bool]:

@@ -117,3 +117,22 @@ def test_per_dimension_transport_switches(monkeypatch):
     monkeypatch.setenv("IGG_B200_TRANSPORT_DIMZ", "mpi")
     with pytest.raises(ValueError):
         per_dim_staging("nccl")
+
+
+def test_default_transport_leaves_the_node_over_nccl(monkeypatch):
+    """Peer mappings are CUDA IPC (one node); a job that spans nodes defaults to the NCCL transport."""
+    import types
+    from rocm_mpi_b200.parallel.comm import spans_nodes
+    from rocm_mpi_b200.parallel.halo import default_transport
+    dev_field, cpu_field = types.SimpleNamespace(is_cuda=True), types.SimpleNamespace(is_cuda=False)
+    monkeypatch.delenv("IGG_B200_TRANSPORT", raising=False)
+    monkeypatch.setenv("WORLD_SIZE", "8")
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "8")
+    assert not spans_nodes() and default_transport(dev_field) == "peer"
+    monkeypatch.setenv("WORLD_SIZE", "16")
+    assert spans_nodes() and default_transport(dev_field) == "nccl"
+    assert default_transport(cpu_field) == "gloo"
+    monkeypatch.setenv("IGG_B200_TRANSPORT", "host")
+    assert default_transport(dev_field) == "host"
+    monkeypatch.delenv("LOCAL_WORLD_SIZE")
+    assert not spans_nodes()                         # no launcher information: assume one node
