@@ -152,14 +152,21 @@ def main() -> int:
     e2e = None
     if not a.no_e2e:
         s.begin()
+        pair = a.impl == "temporal"          # experimental: the host hands over / reads back two steps at a time
         for _ in range(W):
-            s.step_controlled()
+            s.step_controlled_pair() if pair else s.step_controlled()
         g.comm.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         mx = 0.0
-        for _ in range(K):
-            mx, sm = s.step_controlled()
+        if pair:
+            for _ in range(K // 2):
+                _, (mx, sm) = s.step_controlled_pair()
+            for _ in range(K % 2):
+                mx, sm = s.step_controlled()
+        else:
+            for _ in range(K):
+                mx, sm = s.step_controlled()
         torch.cuda.synchronize()
         dt_wall = time.perf_counter() - t0
         g.comm.barrier()
@@ -168,7 +175,7 @@ def main() -> int:
         e2e = {"value": round(nprocs * A_eff / (ms_e2e * 1e-3), 2), "unit": "GB/s", "ms_per_step": round(ms_e2e, 5),
                "h2d_bytes_per_step": Diffusion2D.h2d_bytes_per_step,
                "d2h_bytes_per_step": Diffusion2D.d2h_bytes_per_step, "last_max_T": mx,
-               "api": "rocm_mpi_b200.models.solver.Diffusion2D.step_controlled"}
+               "api": "rocm_mpi_b200.models.solver.Diffusion2D." + ("step_controlled_pair" if pair else "step_controlled")}
     clocks = sampler.stop() if sampler is not None else None
 
     if me == 0:

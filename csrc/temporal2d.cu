@@ -34,11 +34,20 @@ using namespace igg_t2;
 
 constexpr int T2_SMEM_BYTES = RING_PAD * 8 + RING_DOUBLES * 8 + RING_PAD * 8 + 128;   // pad | rings | pad | mbarriers
 
+// block partials + ticket of the optional diagnostic {max, sum} of step k+1 and of step k+2
+struct DiagScratch2 {
+    unsigned int ticket;
+    unsigned int pad[3];
+    double part[4][1024];          // [max1, sum1, max2, sum2][CTA]
+};
+
 struct T2Params {
     double* T2;
     Geom g;
     Phys ph;
-    const double* dev_params;      // optional {lam, dt, _dx, _dy} in device memory
+    const double* dev_params;      // optional {lam, dt, _dx, _dy} x 2 (step k+1, step k+2) in device memory
+    double* diag_out;              // optional {max1, sum1, max2, sum2}
+    DiagScratch2* diag;
     MidLines ml;
     const uint64_t* mid_flag[4];   // my mid flags, one per line (xlo, xhi, ylo, yhi); NULL = no neighbour
     int has_push;
@@ -124,13 +133,13 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
     // ===== consumers ====================================================================================
     const int cp = tid % NPAIR;   // column pair
     const int rg = tid / NPAIR;   // row group inside a block
-    Phys ph = p.ph;
+    Phys ph1 = p.ph, ph2 = p.ph;   // step k+1 / step k+2 (a host control loop may change lam, dt per step)
     if (p.dev_params) {
-        ph.lam = p.dev_params[0];
-        ph.dt = p.dev_params[1];
-        ph._dx = p.dev_params[2];
-        ph._dy = p.dev_params[3];
+        ph1.lam = p.dev_params[0]; ph1.dt = p.dev_params[1]; ph1._dx = p.dev_params[2]; ph1._dy = p.dev_params[3];
+        ph2.lam = p.dev_params[4]; ph2.dt = p.dev_params[5]; ph2._dx = p.dev_params[6]; ph2._dy = p.dev_params[7];
     }
+    const bool diag = p.diag_out != nullptr;
+    double d1max = -INFINITY, d1sum = 0.0, d2max = -INFINITY, d2sum = 0.0;
     unsigned tq = 0, cq = 0, mq = 0;
 
     for (int k = 0; k < n_my; ++k) {
@@ -154,14 +163,22 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
             const double* prevM = ringM + ((qm + SNM - 1) % SNM) * BLK;
             const int xb = it.xin0 + b * SRB;
 
-            step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, nx, ny, ph, p.ml);
+            double oA[RPT], oB[RPT];
+            unsigned wA, wB;
+            step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, nx, ny, ph1, p.ml, oA, oB);
+            if (diag) {
+                step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, ny, wA, wB);
+#pragma unroll
+                for (int r = 0; r < RPT; ++r) {
+                    if ((wA >> r) & 1u) { d1max = fmax(d1max, oA[r]); d1sum += oA[r]; }
+                    if ((wB >> r) & 1u) { d1max = fmax(d1max, oB[r]); d1sum += oB[r]; }
+                }
+            }
             __syncwarp();
             if ((tid & 31) == 0 && b > 0) mbar_arrive_(&emptyT[(qb + SNT - 1) % SNT]);   // T block b-1 is done
             consumer_sync_(CONSUMERS);                                                   // mid block b complete
 
-            double oA[RPT], oB[RPT];
-            unsigned wA, wB;
-            step2_rows<RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, ny, ph, oA, oB, wA, wB);
+            step2_rows<RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, ny, ph2, oA, oB, wA, wB);
 #pragma unroll
             for (int r = 0; r < RPT; ++r) {
                 const bool a = (wA >> r) & 1u, c = (wB >> r) & 1u;
@@ -177,6 +194,10 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                     if (edge_tile) {
                         if (a) push_cell_2d(p.push, nx, ny, x, y, oA[r]);
                         if (c) push_cell_2d(p.push, nx, ny, x, y + 1, oB[r]);
+                    }
+                    if (diag) {
+                        if (a) { d2max = fmax(d2max, oA[r]); d2sum += oA[r]; }
+                        if (c) { d2max = fmax(d2max, oB[r]); d2sum += oB[r]; }
                     }
                 }
             }
@@ -194,6 +215,58 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         if (edge_tile) {
             consumer_sync_(CONSUMERS);   // every remote store of this item has been issued
             if (tid == 0) signal_edges_2d(p.push, p.edge_tiles, e_xl, e_xh, e_yl, e_yh);
+        }
+    }
+
+    // optional diagnostic: CTA partials -> scratch; the last CTA (ticket) folds all partials in a fixed order
+    if (diag) {
+        __shared__ double red[4][32];
+        __shared__ bool is_last;
+        double v[4] = {d1max, d1sum, d2max, d2sum};
+        auto block_fold = [&]() {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) {
+                    const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
+                    v[q] = (q & 1) ? v[q] + o : fmax(v[q], o);
+                }
+            if ((tid & 31) == 0)
+                for (int q = 0; q < 4; ++q) red[q][tid >> 5] = v[q];
+            consumer_sync_(CONSUMERS);
+            if (tid < 32) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    v[q] = tid < NCW ? red[q][tid] : ((q & 1) ? 0.0 : -INFINITY);
+#pragma unroll
+                    for (int off = 16; off > 0; off >>= 1) {
+                        const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
+                        v[q] = (q & 1) ? v[q] + o : fmax(v[q], o);
+                    }
+                }
+            }
+            consumer_sync_(CONSUMERS);
+        };
+        block_fold();
+        if (tid == 0) {
+            for (int q = 0; q < 4; ++q) p.diag->part[q][blockIdx.x] = v[q];
+            __threadfence();
+            is_last = atomicAdd(&p.diag->ticket, 1u) == gridDim.x - 1;
+        }
+        consumer_sync_(CONSUMERS);
+        if (is_last) {
+            __threadfence();
+            for (int q = 0; q < 4; ++q) v[q] = (q & 1) ? 0.0 : -INFINITY;
+            for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS)
+                for (int q = 0; q < 4; ++q) {
+                    const double o = p.diag->part[q][b2];
+                    v[q] = (q & 1) ? v[q] + o : fmax(v[q], o);
+                }
+            block_fold();
+            if (tid == 0) {
+                for (int q = 0; q < 4; ++q) p.diag_out[q] = v[q];
+                p.diag->ticket = 0;
+            }
         }
     }
 }
@@ -261,6 +334,10 @@ static int launch_t2(const CUtensorMap& mT, const CUtensorMap& mC, const T2Param
     const int sms = igg::sm_count();
     const int nitems = num_items(p.g);
     const int grid = nitems < sms ? nitems : sms;
+    if (grid > 1024) {
+        igg::set_error("igg_diffusion2d_step2: more than 1024 CTAs (%d) do not fit the diagnostic scratch", grid);
+        return IGG_ERR_UNSUPPORTED;
+    }
     kern<<<grid, NPAIR*(SRB / RPT) + 32, T2_SMEM_BYTES, st>>>(mT, mC, p);
     return 0;
 }
@@ -276,8 +353,10 @@ extern "C" int igg_temporal2d_default_rows(void) {
     return v;
 }
 
+extern "C" size_t igg_temporal2d_diag_scratch_bytes(void) { return sizeof(DiagScratch2); }
+
 extern "C" int igg_diffusion2d_step2(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
-                                     double dt, double _dx, double _dy, const double* dev_params,
+                                     double dt, double _dx, double _dy, const igg_step_opts* opts,
                                      const igg_push2d* push, const igg_mid2d* mid, void* stream) {
     IGG_REQUIRE(T && T2 && Cp, "igg_diffusion2d_step2: null field pointer");
     IGG_REQUIRE(nx >= 3 && ny >= 4, "igg_diffusion2d_step2: need nx >= 3, ny >= 4 (got %d x %d)", nx, ny);
@@ -292,7 +371,10 @@ extern "C" int igg_diffusion2d_step2(const double* T, double* T2, const double* 
     p.T2 = T2;
     p.g = make_geom(nx, ny, igg_temporal2d_default_rows(), push ? 1 : 0);
     p.ph.lam = lam; p.ph.dt = dt; p.ph._dx = _dx; p.ph._dy = _dy;
-    p.dev_params = dev_params;
+    p.dev_params = opts ? opts->dev_params : nullptr;
+    p.diag_out = opts ? opts->diag_out : nullptr;
+    p.diag = opts ? (DiagScratch2*)opts->diag_scratch : nullptr;
+    IGG_REQUIRE(!p.diag_out || p.diag, "igg_diffusion2d_step2: diag_out needs diag_scratch");
     p.has_push = push ? 1 : 0;
     for (int sx = -1; sx <= 1; ++sx)
         for (int sy = -1; sy <= 1; ++sy)
@@ -366,5 +448,38 @@ extern "C" int igg_diffusion2d_midlines(const double* T, const double* Cp, int n
     dim3 grid(MID_CTAS_PER_FACE, 4);
     diff2d_midlines_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+// One end-to-end PAIR of steps of a host control loop: H2D copy of both steps' {lam, dt, _dx, _dy} (64 B) from
+// pinned host memory, [mid lines to the neighbours,] the two-step pass with both in-kernel diagnostics, D2H copy
+// of {max1, sum1, max2, sum2} (32 B) into pinned host memory; returns when they have arrived.
+extern "C" int igg_diffusion2d_step2_controlled(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                                const double* params_host_pinned, double* params_dev,
+                                                double* diag_dev, void* diag_scratch, double* diag_host_pinned,
+                                                const igg_push2d* push, const igg_mid2d* mid, void* stream) {
+    IGG_REQUIRE(params_host_pinned && params_dev && diag_dev && diag_scratch && diag_host_pinned,
+                "igg_diffusion2d_step2_controlled: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    IGG_CUDA_OK(cudaMemcpyAsync(params_dev, params_host_pinned, 8 * sizeof(double), cudaMemcpyHostToDevice, st));
+    int rc = 0;
+    if (push) {
+        rc = igg_diffusion2d_midlines(T, Cp, nx, ny, 0.0, 0.0, 0.0, 0.0, params_dev, push, mid, stream);
+        if (rc) return rc;
+    }
+    igg_step_opts o;
+    o.dev_params = params_dev;
+    o.diag_out = diag_dev;
+    o.diag_scratch = diag_scratch;
+    rc = igg_diffusion2d_step2(T, T2, Cp, nx, ny, 0.0, 0.0, 0.0, 0.0, &o, push, mid, stream);
+    if (rc) return rc;
+    IGG_CUDA_OK(cudaMemcpyAsync(diag_host_pinned, diag_dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    static thread_local cudaEvent_t ev = nullptr;
+    if (!ev) IGG_CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    IGG_CUDA_OK(cudaEventRecord(ev, st));
+    cudaError_t q;
+    while ((q = cudaEventQuery(ev)) == cudaErrorNotReady) {
+    }
+    IGG_CUDA_OK(q);
     return 0;
 }

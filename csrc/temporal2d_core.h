@@ -172,10 +172,11 @@ T2_HD Item make_item(const Geom& g, int t) {
 // Thread (cp, rg) owns box columns 2cp, 2cp+1 and the block rows rg*RPT ... rg*RPT+RPT-1.
 // prevT / nextT: blocks b-1 / b+1 (any readable block when they do not exist: the rows that would need them
 // are never used).  xb = global row of the block's row 0.
+// The mid values are also returned (mA/mB, row r of the thread) for the optional step-(k+1) diagnostic.
 template <int RPT>
 T2_HD void step1_rows(const double* prevT, const double* curT, const double* nextT, const double* curC,
                       double* curM, int cp, int rg, int xb, int yb, int nx, int ny, const Phys& ph,
-                      const MidLines& ml) {
+                      const MidLines& ml, double (&oA)[RPT], double (&oB)[RPT]) {
     const int col = 2 * cp;
     const int l0 = rg * RPT;
     const double* r_m1 = l0 > 0 ? curT + (l0 - 1) * BW : prevT + (SRB - 1) * BW;
@@ -200,8 +201,30 @@ T2_HD void step1_rows(const double* prevT, const double* curT, const double* nex
         if (!(vx && vy0)) mA = boundary_mid(ml, x, y, nx, ny, bb.x);
         if (!(vx && vy1)) mB = boundary_mid(ml, x, y + 1, nx, ny, bb.y);
         st2(curM + l * BW + col, mA, mB);
+        oA[r] = mA;
+        oB[r] = mB;
         a = bb;
         bb = c;
+    }
+}
+
+// Which of the thread's step-1 cells belong to the item's OWN output region (every interior cell of the array
+// is in exactly one item's region, while mid values are computed redundantly near item borders): bit r of the
+// masks = row r.  Used to attribute the step-(k+1) diagnostic without double counting.
+template <int RPT>
+T2_HD void step1_own_masks(int cp, int rg, int xb, int yb, int x_lo, int x_hi, int ny, unsigned& wA, unsigned& wB) {
+    const int y = yb + 2 * cp;
+    const bool pair_ok = cp >= 1 && cp <= NPAIR - 2;
+    const bool vy0 = pair_ok && y >= 1 && y <= ny - 2;
+    const bool vy1 = pair_ok && y + 1 >= 1 && y + 1 <= ny - 2;
+    wA = 0u;
+    wB = 0u;
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) {
+        const int x = xb + rg * RPT + r;
+        const bool vx = x >= x_lo && x <= x_hi;
+        if (vx && vy0) wA |= 1u << r;
+        if (vx && vy1) wB |= 1u << r;
     }
 }
 

@@ -5,6 +5,7 @@
 // a GPU: a "worker" plays one persistent CTA with its own ring counters, the TMA box load is a copy with zero
 // fill, and the consumer barrier between step 1 and step 2 becomes two loops over the threads.
 // No counterpart in the reference (it has neither native code nor a multi-step kernel).
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -29,8 +30,9 @@ void load_box(const double* A, int nx, int ny, int x, int y, double* dst) {
 }
 
 template <int RPT>
-void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const Phys& ph, int workers,
-             const MidLines& ml) {
+void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const Phys& ph1, const Phys& ph2,
+             int workers, const MidLines& ml, double* diag) {
+    double d1max = -HUGE_VAL, d1sum = 0.0, d2max = -HUGE_VAL, d2sum = 0.0;
     constexpr int NRG = SRB / RPT;
     const int nitems = num_items(g);
     // 16-byte aligned rings, poisoned so that a read of a slot that was never filled shows up
@@ -65,20 +67,36 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
                 const double* prevM = ringM + ((qm + SNM - 1) % SNM) * BLK;
                 const int xb = it.xin0 + b * SRB;
                 for (int rg = 0; rg < NRG; ++rg)
-                    for (int cp = 0; cp < NPAIR; ++cp)
-                        step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, g.nx, g.ny, ph, ml);
+                    for (int cp = 0; cp < NPAIR; ++cp) {
+                        double mA[RPT], mB[RPT];
+                        unsigned wA, wB;
+                        step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, g.nx, g.ny, ph1, ml, mA, mB);
+                        step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, g.ny, wA, wB);
+                        for (int r = 0; r < RPT; ++r) {
+                            if ((wA >> r) & 1u) { d1max = mA[r] > d1max ? mA[r] : d1max; d1sum += mA[r]; }
+                            if ((wB >> r) & 1u) { d1max = mB[r] > d1max ? mB[r] : d1max; d1sum += mB[r]; }
+                        }
+                    }
                 // ---- consumer barrier ----
                 for (int rg = 0; rg < NRG; ++rg)
                     for (int cp = 0; cp < NPAIR; ++cp) {
                         double oA[RPT], oB[RPT];
                         unsigned wA, wB;
-                        step2_rows<RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, g.ny, ph, oA, oB,
+                        step2_rows<RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, g.ny, ph2, oA, oB,
                                         wA, wB);
                         const int y = it.yb + 2 * cp;
                         for (int r = 0; r < RPT; ++r) {
                             const int x = xb - 1 + rg * RPT + r;
-                            if ((wA >> r) & 1u) T2[(size_t)x * g.ny + y] = oA[r];
-                            if ((wB >> r) & 1u) T2[(size_t)x * g.ny + y + 1] = oB[r];
+                            if ((wA >> r) & 1u) {
+                                T2[(size_t)x * g.ny + y] = oA[r];
+                                d2max = oA[r] > d2max ? oA[r] : d2max;
+                                d2sum += oA[r];
+                            }
+                            if ((wB >> r) & 1u) {
+                                T2[(size_t)x * g.ny + y + 1] = oB[r];
+                                d2max = oB[r] > d2max ? oB[r] : d2max;
+                                d2sum += oB[r];
+                            }
                         }
                     }
             }
@@ -87,13 +105,20 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
             mq += it.nbi;
         }
     }
+    if (diag) {
+        diag[0] = d1max;
+        diag[1] = d1sum;
+        diag[2] = d2max;
+        diag[3] = d2sum;
+    }
 }
 
 }  // namespace
 
 extern "C" int igg_cpu_temporal2d_emulate(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
                                           double dt, double _dx, double _dy, int scx, int rpt, int workers,
-                                          const double* mid_lines, int side_mask) {
+                                          const double* mid_lines, int side_mask, const double* phys2,
+                                          double* diag_out) {
     if (!T || !T2 || !Cp || nx < 3 || ny < 4 || (ny & 1)) return IGG_ERR_INVALID;
     if (scx < SRB - 4 || (scx + 4) % SRB || workers < 1 || (rpt != 2 && rpt != 4)) return IGG_ERR_INVALID;
     if (side_mask && !mid_lines) return IGG_ERR_INVALID;
@@ -108,8 +133,15 @@ extern "C" int igg_cpu_temporal2d_emulate(const double* T, double* T2, const dou
     ml.xhi = (side_mask & 2) ? mid_lines + mid_line_offset(1, nx, ny) : nullptr;
     ml.ylo = (side_mask & 4) ? mid_lines + mid_line_offset(2, nx, ny) : nullptr;
     ml.yhi = (side_mask & 8) ? mid_lines + mid_line_offset(3, nx, ny) : nullptr;
-    if (rpt == 4) emulate<4>(T, T2, Cp, g, ph, workers, ml);
-    else emulate<2>(T, T2, Cp, g, ph, workers, ml);
+    Phys ph2 = ph;
+    if (phys2) {
+        ph2.lam = phys2[0];
+        ph2.dt = phys2[1];
+        ph2._dx = phys2[2];
+        ph2._dy = phys2[3];
+    }
+    if (rpt == 4) emulate<4>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
+    else emulate<2>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
     return 0;
 }
 

@@ -148,9 +148,20 @@ typedef struct igg_mid2d {
     uint64_t* my_count[4];          /* private CTA arrival counters (monotonic)                              */
 } igg_mid2d;
 #define IGG_SLOT_MID 56             /* flag pad: mid flags of sides 0..3; counter pad: their CTA counters     */
+/* `opts` (may be NULL): dev_params = device array of EIGHT doubles, {lam, dt, _dx, _dy} of step k+1 then of step
+ * k+2; diag_out = device array of FOUR doubles {max, sum} of step k+1 and {max, sum} of step k+2 over the
+ * halo-free interior; diag_scratch = igg_temporal2d_diag_scratch_bytes() bytes, zero-filled once. */
 int igg_diffusion2d_step2(const double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
-                          double _dx, double _dy, const double* dev_params, const igg_push2d* push,
+                          double _dx, double _dy, const igg_step_opts* opts, const igg_push2d* push,
                           const igg_mid2d* mid, void* stream);
+size_t igg_temporal2d_diag_scratch_bytes(void);
+/* One end-to-end PAIR of steps of a host control loop: H2D copy of both steps' parameters (64 B, pinned), mid
+ * lines, the pass with both diagnostics, D2H copy of the four diagnostic values (32 B, pinned); the stream has
+ * been waited for on return.  The host decides every two steps instead of every step. */
+int igg_diffusion2d_step2_controlled(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                     const double* params_host_pinned, double* params_dev, double* diag_dev,
+                                     void* diag_scratch, double* diag_host_pinned, const igg_push2d* push,
+                                     const igg_mid2d* mid, void* stream);
 int igg_diffusion2d_midlines(const double* T, const double* Cp, int nx, int ny, double lam, double dt, double _dx,
                              double _dy, const double* dev_params, const igg_push2d* push, const igg_mid2d* mid,
                              void* stream);
@@ -162,7 +173,8 @@ int igg_temporal2d_default_rows(void);
  * exists on side s.  igg_cpu_temporal2d_midlines fills the neighbours' buffers (`peer_mid[s]`, NULL = none). */
 int igg_cpu_temporal2d_emulate(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
                                double dt, double _dx, double _dy, int scx, int rpt, int workers,
-                               const double* mid_lines, int side_mask);
+                               const double* mid_lines, int side_mask, const double* phys2 /* step k+2, or NULL */,
+                               double* diag_out /* {max1, sum1, max2, sum2} or NULL */);
 int igg_cpu_temporal2d_midlines(const double* T, const double* Cp, int nx, int ny, double lam, double dt,
                                 double _dx, double _dy, double* const* peer_mid);
 

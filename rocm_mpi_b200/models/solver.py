@@ -109,6 +109,11 @@ class Diffusion2D:
         self._params_pin = torch.zeros(4, dtype=torch.float64).pin_memory()
         self._diag_dev = torch.zeros(2, dtype=torch.float64, device=dev)
         self._diag_pin = torch.zeros(2, dtype=torch.float64).pin_memory()
+        if mode == "temporal":       # a pass hands over two steps' parameters and returns two diagnostics
+            self._params2_dev = torch.zeros(8, dtype=torch.float64, device=dev)
+            self._params2_pin = torch.zeros(8, dtype=torch.float64).pin_memory()
+            self._diag2_dev = torch.zeros(4, dtype=torch.float64, device=dev)
+            self._diag2_pin = torch.zeros(4, dtype=torch.float64).pin_memory()
 
     # -- set-up -----------------------------------------------------------------------------------
     def _init_condition(self, host_ic: bool) -> None:
@@ -288,6 +293,28 @@ class Diffusion2D:
         self._diag_pin.copy_(self._diag_dev, non_blocking=True)        # D2H, 16 bytes
         torch.cuda.current_stream().synchronize()
         return float(self._diag_pin[0]), float(self._diag_pin[1])
+
+    def step_controlled_pair(self, lam: Optional[Sequence[float]] = None, dt: Optional[Sequence[float]] = None):
+        """``mode='temporal'``: one end-to-end PAIR of steps.  The host hands over both steps' parameters in pinned
+        memory (64 B) and reads back ``((max, sum) after step k+1, (max, sum) after step k+2)`` (32 B); it decides
+        every two steps instead of every step.  Experimental like the mode itself."""
+        if self.mode != "temporal":
+            raise ValueError("step_controlled_pair needs mode='temporal'")
+        if not self._running:
+            self.begin()
+        p = self._params2_pin
+        for k in range(2):
+            p[4 * k + 0] = self.lam if lam is None else lam[k]
+            p[4 * k + 1] = self.dt if dt is None else dt[k]
+            p[4 * k + 2] = self._dx
+            p[4 * k + 3] = self._dy
+        push = self.plan.next(self.T2, two_step=True)
+        native.diffusion2d_step2_controlled(self.T2, self.T, self.Cp, p, self._params2_dev, self._diag2_dev,
+                                            self._diag2_pin, push=push, mid=self._mid if push is not None else None)
+        self.T, self.T2 = self.T2, self.T
+        self.steps_done += 2
+        d = self._diag2_pin
+        return (float(d[0]), float(d[1])), (float(d[2]), float(d[3]))
 
     @property
     def fused_diag(self) -> bool:

@@ -106,10 +106,14 @@ def _declare(lib) -> None:
         "igg_cpu_residual2d": ([vp, vp, vp, vp, i, i, d, d], i),
         "igg_cpu_update2d": ([vp, vp, i, i, d], i),
         "igg_cpu_diffusion3d_step": ([vp, vp, vp, i, i, i, d, d, d, d, d], i),
-        "igg_diffusion2d_step2": ([vp, vp, vp, i, i, d, d, d, d, vp, C.POINTER(Push2D), C.POINTER(Mid2D), vp], i),
+        "igg_diffusion2d_step2": ([vp, vp, vp, i, i, d, d, d, d, C.POINTER(StepOpts), C.POINTER(Push2D),
+                                  C.POINTER(Mid2D), vp], i),
+        "igg_temporal2d_diag_scratch_bytes": ([], sz),
+        "igg_diffusion2d_step2_controlled": ([vp, vp, vp, i, i, vp, vp, vp, vp, vp, C.POINTER(Push2D),
+                                             C.POINTER(Mid2D), vp], i),
         "igg_diffusion2d_midlines": ([vp, vp, i, i, d, d, d, d, vp, C.POINTER(Push2D), C.POINTER(Mid2D), vp], i),
         "igg_temporal2d_default_rows": ([], i),
-        "igg_cpu_temporal2d_emulate": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, vp, i], i),
+        "igg_cpu_temporal2d_emulate": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, vp, i, vp, vp], i),
         "igg_cpu_temporal2d_midlines": ([vp, vp, i, i, d, d, d, d, C.POINTER(vp)], i),
     }
     for name, (argtypes, restype) in sig.items():
@@ -213,20 +217,64 @@ def diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: f
                                     C.byref(push) if push is not None else None, _stream()))
 
 
+_t2_scratch = {}
+
+
+def _temporal_scratch(device: torch.device) -> torch.Tensor:
+    """Zero-filled once; the two-step kernel leaves it ready for the next launch."""
+    key = device.index
+    if key not in _t2_scratch:
+        n = int(require().igg_temporal2d_diag_scratch_bytes())
+        _t2_scratch[key] = torch.zeros((n + 7) // 8, dtype=torch.int64, device=device)
+    return _t2_scratch[key]
+
+
 def diffusion2d_step2(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
                       _dy: float, push: Optional[Push2D] = None, mid: Optional["Mid2D"] = None,
-                      dev_params: Optional[torch.Tensor] = None) -> None:
+                      dev_params: Optional[torch.Tensor] = None, diag_out: Optional[torch.Tensor] = None) -> None:
     """``T2 <- step(step(T))`` in one pass over memory (``igg_diffusion2d_step2``).  With neighbours, call
-    :func:`diffusion2d_midlines` with the same descriptors first (see ``parallel/fabric.py:PushPlan2``).
+    :func:`diffusion2d_midlines` with the same descriptors first (``PushPlan.mid_lines()``).
+    ``dev_params``: device tensor of 8 doubles (``[lam, dt, _dx, _dy]`` of step k+1, then of step k+2);
+    ``diag_out``: device tensor of 4 doubles receiving ``[max, sum]`` of step k+1 and of step k+2.
     Experimental: validated through the host emulator only (:func:`cpu_temporal2d_emulate`)."""
     lib = require()
     nx, ny = T.shape
     if T2.shape != T.shape or Cp.shape != T.shape:
         raise ValueError("T, T2 and Cp must have the same shape")
+    opts = None
+    if dev_params is not None or diag_out is not None:
+        opts = StepOpts()
+        if dev_params is not None:
+            if dev_params.numel() < 8:
+                raise ValueError("dev_params of the two-step kernel holds 8 doubles (two steps)")
+            opts.dev_params = _f64(dev_params, "dev_params")
+        if diag_out is not None:
+            if diag_out.numel() < 4:
+                raise ValueError("diag_out of the two-step kernel holds 4 doubles")
+            opts.diag_out = _f64(diag_out, "diag_out")
+            opts.diag_scratch = _temporal_scratch(T.device).data_ptr()
     _check(lib.igg_diffusion2d_step2(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
-                                     _f64(dev_params, "dev_params") if dev_params is not None else None,
+                                     C.byref(opts) if opts is not None else None,
                                      C.byref(push) if push is not None else None,
                                      C.byref(mid) if mid is not None else None, _stream()))
+
+
+def diffusion2d_step2_controlled(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, params_pin: torch.Tensor,
+                                 params_dev: torch.Tensor, diag_dev: torch.Tensor, diag_pin: torch.Tensor,
+                                 push: Optional[Push2D] = None, mid: Optional["Mid2D"] = None) -> None:
+    """One end-to-end pair of steps from native code (``igg_diffusion2d_step2_controlled``): H2D of 8 parameters,
+    mid lines, two-step pass, D2H of the 4 diagnostic values; returns after they have arrived in ``diag_pin``."""
+    lib = require()
+    nx, ny = T.shape
+    if not (params_pin.is_pinned() and diag_pin.is_pinned()):
+        raise TypeError("params_pin and diag_pin must be pinned host tensors")
+    if params_pin.numel() < 8 or params_dev.numel() < 8 or diag_dev.numel() < 4 or diag_pin.numel() < 4:
+        raise ValueError("need 8 parameter doubles and 4 diagnostic doubles")
+    _check(lib.igg_diffusion2d_step2_controlled(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny,
+                                                params_pin.data_ptr(), _f64(params_dev), _f64(diag_dev),
+                                                _temporal_scratch(T.device).data_ptr(), diag_pin.data_ptr(),
+                                                C.byref(push) if push is not None else None,
+                                                C.byref(mid) if mid is not None else None, _stream()))
 
 
 def diffusion2d_midlines(T: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float, _dy: float,
@@ -458,7 +506,8 @@ def temporal2d_default_rows() -> int:
 
 def cpu_temporal2d_emulate(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam, dt, _dx, _dy, scx: int = 252,
                            rpt: int = 2, workers: int = 148, mid_lines: Optional[torch.Tensor] = None,
-                           side_mask: int = 0) -> None:
+                           side_mask: int = 0, phys2: Optional[Sequence[float]] = None,
+                           diag_out: Optional[torch.Tensor] = None) -> None:
     """Run the index code of the two-steps-per-pass CUDA kernel on the host, thread by thread
     (``igg_cpu_temporal2d_emulate``): ``T2 <- step(step(T))`` on the cells that kernel writes."""
     lib = require()
@@ -468,9 +517,14 @@ def cpu_temporal2d_emulate(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, 
     nx, ny = T.shape
     if mid_lines is not None and mid_lines.numel() < 2 * nx + 2 * ny:
         raise ValueError("mid_lines needs 2*nx + 2*ny elements")
+    p2 = (C.c_double * 4)(*[float(v) for v in phys2]) if phys2 is not None else None
+    if diag_out is not None and (diag_out.is_cuda or diag_out.dtype != torch.float64 or diag_out.numel() < 4):
+        raise TypeError("diag_out must be a CPU float64 tensor of 4 elements")
     _check(lib.igg_cpu_temporal2d_emulate(T.data_ptr(), T2.data_ptr(), Cp.data_ptr(), nx, ny, lam, dt, _dx, _dy,
                                           scx, rpt, workers,
-                                          mid_lines.data_ptr() if mid_lines is not None else None, side_mask))
+                                          mid_lines.data_ptr() if mid_lines is not None else None, side_mask,
+                                          C.cast(p2, C.c_void_p) if p2 is not None else None,
+                                          diag_out.data_ptr() if diag_out is not None else None))
 
 
 def cpu_temporal2d_midlines(T: torch.Tensor, Cp: torch.Tensor, lam, dt, _dx, _dy,

@@ -53,6 +53,29 @@ def through_solver(nx, ny, periods, nsteps):
     return float((out["fused"] - out["temporal"]).abs().max())
 
 
+def controlled_pairs(nx, ny, periods, npairs):
+    """step_controlled_pair against single controlled steps of the fused mode: field and both diagnostics."""
+    igg.init_global_grid(nx, ny, 1, periodx=periods[0], periody=periods[1], quiet=True)
+    s = Diffusion2D(nx, ny, mode="fused")
+    want = []
+    for _ in range(2 * npairs):
+        want.append(s.step_controlled())
+    s.finish()
+    Tf = s.T.clone()
+    igg.finalize_global_grid()
+    igg.init_global_grid(nx, ny, 1, periodx=periods[0], periody=periods[1], quiet=True)
+    s = Diffusion2D(nx, ny, mode="temporal")
+    got = []
+    for _ in range(npairs):
+        d1, d2 = s.step_controlled_pair()
+        got += [d1, d2]
+    s.finish()
+    err = float((s.T - Tf).abs().max())
+    igg.finalize_global_grid()
+    derr = max(max(abs(g[0] - w[0]), abs(g[1] - w[1]) / max(1.0, abs(w[1]))) for g, w in zip(got, want))
+    return err, derr
+
+
 def timing(nx, ny, steps):
     res = {}
     for mode in ("fused", "temporal"):
@@ -95,6 +118,11 @@ def main():
             err = through_solver(nx, ny, per, n)
             print(f"  {nx} x {ny} periods {per} steps {n}: max |fused - temporal| = {err:.3e}", flush=True)
             ok &= err < 1e-12
+        print("stage 2b: controlled pairs (per-step parameters in, both diagnostics out)", flush=True)
+        for (nx, ny, per) in [(130, 258, (0, 0)), (300, 380, (1, 1))]:
+            err, derr = controlled_pairs(nx, ny, per, 3)
+            print(f"  {nx} x {ny} periods {per}: max |field diff| = {err:.3e}, max diagnostic diff = {derr:.3e}", flush=True)
+            ok &= err < 1e-12 and derr < 1e-9
     else:
         if rank == 0:
             print(f"stage 2: solver on {world} ranks", flush=True)

@@ -124,3 +124,29 @@ def test_frame_first_item_order(dims, periods):
     """With neighbours the items on the array edge come first (they push); needs >= 3 strips and >= 3 tile
     columns to differ from row-major order.  Any item visited twice or not at all breaks the equality."""
     _run_virtual(dims, periods, (44, 380), scx=12, rpt=4, workers=5)
+
+
+@pytest.mark.parametrize("shape,scx,workers", [((40, 126), 12, 3), ((130, 258), 28, 7), ((300, 380), 252, 148)])
+def test_diagnostics_of_both_steps_and_per_step_parameters(shape, scx, workers):
+    """{max, sum} after step k+1 (taken from the mid values, each interior cell attributed to exactly one work
+    item) and after step k+2; the two steps may use different lam / dt (a host control loop changes them)."""
+    T, Cp = _fields(*shape, seed=9)
+    ph1, ph2 = (1.3, 1e-3, 2.0, 3.0), (0.9, 7e-4, 2.0, 3.0)
+    a = T.clone()
+    ref.perf_step(a, T, Cp, *ph1)
+    b = a.clone()
+    ref.perf_step(b, a, Cp, *ph2)
+    T2 = T.clone()
+    diag = torch.zeros(4, dtype=torch.float64)
+    native.cpu_temporal2d_emulate(T2, T, Cp, *ph1, scx=scx, rpt=2, workers=workers, phys2=ph2, diag_out=diag)
+    assert torch.equal(T2, b)
+    ia, ib = a[1:-1, 1:-1], b[1:-1, 1:-1]
+    assert float(diag[0]) == float(ia.max()) and float(diag[2]) == float(ib.max())
+    assert abs(float(diag[1]) - float(ia.sum())) < 1e-9 * ia.numel()
+    assert abs(float(diag[3]) - float(ib.sum())) < 1e-9 * ib.numel()
+    # count check: the sums above only match if no cell is attributed twice or dropped; make it explicit
+    ones = torch.ones_like(T)
+    d2 = torch.zeros(4, dtype=torch.float64)
+    native.cpu_temporal2d_emulate(ones.clone(), ones, torch.ones_like(T), 0.0, 0.0, 1.0, 1.0, scx=scx, rpt=4,
+                                  workers=workers, diag_out=d2)
+    assert float(d2[1]) == float(ia.numel()) and float(d2[3]) == float(ib.numel())
