@@ -148,6 +148,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         const bool e_yl = it.j == 0 && p.side_nb[2], e_yh = it.j == p.g.ntj - 1 && p.side_nb[3];
         const bool edge_tile = p.has_push && (e_xl || e_xh || e_yl || e_yh);
         const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;      // inside [1, nx-2] by construction
+        const bool inner = item_is_inner(p.g, it);
         const int y = it.yb + 2 * cp;
         mbar_wait(&fullT[tq % SNT], (tq / SNT) & 1);
         for (int b = 0; b < it.nbi; ++b) {
@@ -165,7 +166,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
 
             double oA[RPT], oB[RPT];
             unsigned wA, wB;
-            step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, nx, ny, ph1, p.ml, oA, oB);
+            step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, nx, ny, ph1, p.ml, inner, oA, oB);
             if (diag) {
                 step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, ny, wA, wB);
 #pragma unroll

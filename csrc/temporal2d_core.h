@@ -168,6 +168,11 @@ T2_HD Item make_item(const Geom& g, int t) {
     return it;
 }
 
+// does every cell of the item's blocks lie in the updated region [1,nx-2] x [1,ny-2]?
+T2_HD bool item_is_inner(const Geom& g, const Item& it) {
+    return it.xin0 >= 1 && it.xin0 + it.nbi * SRB - 1 <= g.nx - 2 && it.yb >= 1 && it.yb + BW - 1 <= g.ny - 2;
+}
+
 // ---- step 1: mid values of block b --------------------------------------------------------------------
 // Thread (cp, rg) owns box columns 2cp, 2cp+1 and the block rows rg*RPT ... rg*RPT+RPT-1.
 // prevT / nextT: blocks b-1 / b+1 (any readable block when they do not exist: the rows that would need them
@@ -176,7 +181,7 @@ T2_HD Item make_item(const Geom& g, int t) {
 template <int RPT>
 T2_HD void step1_rows(const double* prevT, const double* curT, const double* nextT, const double* curC,
                       double* curM, int cp, int rg, int xb, int yb, int nx, int ny, const Phys& ph,
-                      const MidLines& ml, double (&oA)[RPT], double (&oB)[RPT]) {
+                      const MidLines& ml, bool inner, double (&oA)[RPT], double (&oB)[RPT]) {
     const int col = 2 * cp;
     const int l0 = rg * RPT;
     const double* r_m1 = l0 > 0 ? curT + (l0 - 1) * BW : prevT + (SRB - 1) * BW;
@@ -198,8 +203,10 @@ T2_HD void step1_rows(const double* prevT, const double* curT, const double* nex
         const bool vx = x >= 1 && x <= nx - 2;
         double mA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph);
         double mB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph);
-        if (!(vx && vy0)) mA = boundary_mid(ml, x, y, nx, ny, bb.x);
-        if (!(vx && vy1)) mB = boundary_mid(ml, x, y + 1, nx, ny, bb.y);
+        if (!inner) {      // items whose box lies inside [1,nx-2] x [1,ny-2] (nearly all) skip the boundary rules
+            if (!(vx && vy0)) mA = boundary_mid(ml, x, y, nx, ny, bb.x);
+            if (!(vx && vy1)) mB = boundary_mid(ml, x, y + 1, nx, ny, bb.y);
+        }
         st2(curM + l * BW + col, mA, mB);
         oA[r] = mA;
         oB[r] = mB;

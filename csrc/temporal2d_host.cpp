@@ -52,6 +52,7 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
         for (int k = 0; k < n_my; ++k) {
             const Item it = make_item(g, w + k * workers);
             const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;
+            const bool inner = item_is_inner(g, it);
             load_box(T, g.nx, g.ny, it.xin0, it.yb, ringT + (tq % SNT) * BLK);
             for (int b = 0; b < it.nbi; ++b) {
                 const unsigned qb = tq + b, qc = cq + b, qm = mq + b;
@@ -70,7 +71,7 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
                     for (int cp = 0; cp < NPAIR; ++cp) {
                         double mA[RPT], mB[RPT];
                         unsigned wA, wB;
-                        step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, g.nx, g.ny, ph1, ml, mA, mB);
+                        step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, g.nx, g.ny, ph1, ml, inner, mA, mB);
                         step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, g.ny, wA, wB);
                         for (int r = 0; r < RPT; ++r) {
                             if ((wA >> r) & 1u) { d1max = mA[r] > d1max ? mA[r] : d1max; d1sum += mA[r]; }
