@@ -46,6 +46,15 @@ def test_emulated_kernel_equals_two_steps(shape, rpt):
         assert torch.equal(T2, want), (shape, rpt, scx, workers, float((T2 - want).abs().max()))
 
 
+def test_bench_like_geometry():
+    """Default item height (252 rows), 148 workers, several full strips and a dozen tile columns."""
+    T, Cp = _fields(1100, 1500, seed=4)
+    want = _two_steps(T, Cp)
+    T2 = T.clone()
+    native.cpu_temporal2d_emulate(T2, T, Cp, *PH, scx=native.temporal2d_default_rows(), rpt=2, workers=148)
+    assert torch.equal(T2, want)
+
+
 def test_boundary_cells_are_never_written():
     T, Cp = _fields(70, 260)
     T2 = torch.full_like(T, -7.0)
