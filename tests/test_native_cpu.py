@@ -17,6 +17,8 @@ def test_struct_layouts_match_header():
     assert ctypes.sizeof(native.Push3D) == 27 * 8 * 4 + 16
     assert ctypes.sizeof(native.HaloXfer) == 16 + 4 * 12 + 8
     assert ctypes.sizeof(native.HaloSync) == 27 * 8 + 24
+    assert ctypes.sizeof(native.Mid2D) == 8 + 4 * 4 * 8
+    assert ctypes.sizeof(native.StepOpts) == 24
 
 
 def test_cpu_step_bit_exact_vs_torch():

@@ -14,8 +14,6 @@ from rocm_mpi_b200.ops import reference as ref
 from rocm_mpi_b200.parallel.topology import PROC_NULL
 from rocm_mpi_b200.parallel.virtual import VirtualGrid
 
-pytestmark = pytest.mark.skipif(not native.loaded(), reason="native library not built")
-
 PH = (1.3, 1e-3, 2.0, 3.0)   # lam, dt, 1/dx, 1/dy
 
 
