@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) diff2d_resident_kernel(const _
         if (!ll && has_peers) __syncthreads();
         // ---- announce my pushes: one flag per (neighbour offset, CTA) -------------------------------------
         if (!ll && tid < 9 && tid != 4 && p.peer_flags[tid]) {
-            const int sx = tid / 3 - 1, sy = tid % 3 - 1;
+            const int sx = tid / 3 - 1;
             const bool mine = (sx == -1 ? own_row1 : (sx == 1 ? own_rowN : true)) && nr > 0;
             // y-direction pushes come from every CTA; x-direction / corner pushes only from the row owner
             if (mine) {

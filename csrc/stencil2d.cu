@@ -325,7 +325,6 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
                     const __grid_constant__ CUtensorMap mapCp, const __grid_constant__ Params p) {
     constexpr int CONSUMERS = (BY / 2) * (SRB / RPT);
     constexpr int NCW = CONSUMERS / 32;
-    constexpr int NRG = SRB / RPT;          // row groups per block
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* ringT = smem;
     unsigned char* ringC = smem + SNT * ST_BYTES;

@@ -54,7 +54,7 @@ def _compile(src: str, force: bool, verbose: bool, hdr_m: float) -> str:
         return obj
     cmd = [nvcc(), *ARCH, *NVCC_FLAGS, "-c", src, "-o", obj]
     if src.endswith(".cpp"):
-        cmd = [nvcc(), "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off",
+        cmd = [nvcc(), *ARCH, "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off",
                "-Xcompiler", "-fopenmp", "-I", INC, "-c", src, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = os.path.join(OBJ, os.path.basename(src) + ".log")
