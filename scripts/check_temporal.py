@@ -106,10 +106,14 @@ def main():
     ap.add_argument("--ny", type=int, default=16384)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--skip-timing", action="store_true")
+    ap.add_argument("--timing-only", action="store_true")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     ok = True
+    if a.timing_only:
+        timing(a.nx, a.ny, a.steps)
+        return 0
     if world == 1:
         print("stage 1: kernel alone", flush=True)
         ok &= kernel_alone() < 1e-12
