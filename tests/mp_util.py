@@ -19,6 +19,7 @@ def run_workers(script: str, nprocs: int, args=(), timeout: int = 300, extra_env
     for r in range(nprocs):
         env = dict(os.environ)
         env.update({"RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(nprocs),
+                    "LOCAL_WORLD_SIZE": str(nprocs),
                     "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port),
                     "PYTHONPATH": ROOT + os.pathsep + env.get("PYTHONPATH", ""),
                     "OMP_NUM_THREADS": "1"})
