@@ -46,6 +46,13 @@ def test_perf_apps_on_cpu_over_gloo(nprocs, tmp_path):
     assert all("ok" in o for o in outs)
 
 
+def test_per_rank_before_after_pictures(tmp_path):
+    """The reference's proof-of-concept figure (two ranks, before / after, heat crossing the seam) as files."""
+    outs = run_workers("poc_gloo.py", 2, (str(tmp_path),), timeout=300)
+    assert all("ok" in o for o in outs)
+    assert any("max |halo - neighbour's edge| across x seams = 0.0e+00" in o for o in outs)
+
+
 def test_ring_smoke_test_over_gloo():
     outs = run_workers("ring_gloo.py", 4)
     assert all("ok" in o for o in outs)
