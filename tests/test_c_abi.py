@@ -33,3 +33,14 @@ def test_c_program_reproduces_the_golden_value(tmp_path):
     assert out.returncode == 0, out.stderr
     m = re.search(r"max\(T_v\) = ([0-9.]+)", out.stdout)
     assert m and abs(float(m.group(1)) - 0.3978647302669094) < 1e-15, out.stdout
+
+
+@pytest.mark.skipif(not os.path.exists("/usr/local/cuda/include/cuda_runtime_api.h"), reason="no CUDA toolkit headers")
+def test_gpu_c_example_compiles_and_links(tmp_path):
+    """examples/c/heat_gpu.c (CUDA runtime + the library, no Python) must at least build against the header."""
+    libdir = os.path.dirname(native.lib_path())
+    r = subprocess.run([gcc, "-std=c99", "-O2", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                        "-I", "/usr/local/cuda/include", os.path.join(ROOT, "examples", "c", "heat_gpu.c"),
+                        "-o", str(tmp_path / "heat_gpu"), "-L", libdir, "-ligg_b200", f"-Wl,-rpath,{libdir}",
+                        "-L", "/usr/local/cuda/lib64", "-lcudart"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
