@@ -11,6 +11,8 @@ if ROOT not in sys.path:
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: test needs a CUDA device (run on the B200 box with -m gpu)")
     config.addinivalue_line("markers", "multigpu: test needs >= 2 CUDA devices")
+    config.addinivalue_line("markers", "temporal_gpu: staged GPU tests of the two-steps-per-pass kernel "
+                            "(not part of the gpu tier until the kernel has run on hardware)")
 
 
 @pytest.fixture(scope="session", autouse=True)
