@@ -32,7 +32,7 @@ namespace {
 using namespace igg;
 using namespace igg_t2;
 
-constexpr int T2_SMEM_BYTES = RING_PAD * 8 + RING_DOUBLES * 8 + RING_PAD * 8 + 128;   // pad | rings | pad | mbarriers
+constexpr int t2_smem_bytes(int srb) { return RING_PAD * 8 + ring_doubles(srb) * 8 + RING_PAD * 8 + 128; }  // pad | rings | pad | mbarriers
 
 // block partials + ticket of the optional diagnostic {max, sum} of step k+1 and of step k+2
 struct DiagScratch2 {
@@ -63,12 +63,13 @@ __device__ __forceinline__ void consumer_sync_(int nthreads) {
     asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
 }
 
-template <int RPT>
-__global__ void __launch_bounds__(NPAIR*(SRB / RPT) + 32, 1)
+template <int SRB, int RPT>
+__global__ void __launch_bounds__(NPAIR*(SRB / RPT) + 32, SRB == 8 ? 2 : 1)
 diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapC,
                         const __grid_constant__ T2Params p) {
     constexpr int CONSUMERS = NPAIR * (SRB / RPT);
     constexpr int NCW = CONSUMERS / 32;
+    constexpr int BLK = blk_doubles(SRB), BLK_BYTES = BLK * 8;
     extern __shared__ __align__(128) unsigned char smem[];
     double* ringT = reinterpret_cast<double*>(smem) + RING_PAD;      // 128 B in: still 128-byte aligned for TMA
     double* ringC = ringT + SNT * BLK;
@@ -166,7 +167,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
 
             double oA[RPT], oB[RPT];
             unsigned wA, wB;
-            step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, nx, ny, ph1, p.ml, inner, oA, oB);
+            step1_rows<SRB, RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, nx, ny, ph1, p.ml, inner, oA, oB);
             if (diag) {
                 step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, ny, wA, wB);
 #pragma unroll
@@ -179,7 +180,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
             if ((tid & 31) == 0 && b > 0) mbar_arrive_(&emptyT[(qb + SNT - 1) % SNT]);   // T block b-1 is done
             consumer_sync_(CONSUMERS);                                                   // mid block b complete
 
-            step2_rows<RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, ny, ph2, oA, oB, wA, wB);
+            step2_rows<SRB, RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, ny, ph2, oA, oB, wA, wB);
 #pragma unroll
             for (int r = 0; r < RPT; ++r) {
                 const bool a = (wA >> r) & 1u, c = (wB >> r) & 1u;
@@ -322,9 +323,10 @@ static int env_int_(const char* name, int dflt) {
     return e ? atoi(e) : dflt;
 }
 
-template <int RPT>
+template <int SRB, int RPT>
 static int launch_t2(const CUtensorMap& mT, const CUtensorMap& mC, const T2Params& p, cudaStream_t st) {
-    auto kern = diff2d_temporal2_kernel<RPT>;
+    auto kern = diff2d_temporal2_kernel<SRB, RPT>;
+    constexpr int T2_SMEM_BYTES = t2_smem_bytes(SRB);
     static bool attr_set[64] = {false};
     int dev = 0;
     IGG_CUDA_OK(cudaGetDevice(&dev));
@@ -332,9 +334,9 @@ static int launch_t2(const CUtensorMap& mT, const CUtensorMap& mC, const T2Param
         IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    const int sms = igg::sm_count();
+    const int slots = igg::sm_count() * (SRB == 8 ? 2 : 1);      // 8-row blocks: two CTAs per SM
     const int nitems = num_items(p.g);
-    const int grid = nitems < sms ? nitems : sms;
+    const int grid = nitems < slots ? nitems : slots;
     if (grid > 1024) {
         igg::set_error("igg_diffusion2d_step2: more than 1024 CTAs (%d) do not fit the diagnostic scratch", grid);
         return IGG_ERR_UNSUPPORTED;
@@ -349,7 +351,7 @@ extern "C" int igg_temporal2d_default_rows(void) {
     static int v = -1;
     if (v < 0) {
         v = env_int_("IGG_T2_ROWS", 252);
-        if (v < SRB - 4 || (v + 4) % SRB) v = 252;
+        if (v < 12 || (v + 4) % 16) v = 252;        // (rows + 4) must be a multiple of the block height (8 or 16)
     }
     return v;
 }
@@ -370,7 +372,12 @@ extern "C" int igg_diffusion2d_step2(const double* T, double* T2, const double* 
     T2Params p;
     memset(&p, 0, sizeof(p));
     p.T2 = T2;
-    p.g = make_geom(nx, ny, igg_temporal2d_default_rows(), push ? 1 : 0);
+    static int srb = -1, rpt = -1;
+    if (srb < 0) {
+        srb = env_int_("IGG_T2_SRB", 16) == 8 ? 8 : 16;
+        rpt = env_int_("IGG_T2_RPT", 2) == 4 ? 4 : 2;
+    }
+    p.g = make_geom(nx, ny, srb, igg_temporal2d_default_rows(), push ? 1 : 0);
     p.ph.lam = lam; p.ph.dt = dt; p.ph._dx = _dx; p.ph._dy = _dy;
     p.dev_params = opts ? opts->dev_params : nullptr;
     p.diag_out = opts ? opts->diag_out : nullptr;
@@ -407,16 +414,16 @@ extern "C" int igg_diffusion2d_step2(const double* T, double* T2, const double* 
     }
     CUtensorMap mT, mC;
     const uint64_t dims[2] = {(uint64_t)ny, (uint64_t)nx};
-    const uint32_t box[2] = {BW, SRB};
+    const uint32_t box[2] = {BW, (uint32_t)srb};
     int rc = igg::get_tensor_map_f64(T, 2, dims, box, &mT);
     if (rc) return rc;
     rc = igg::get_tensor_map_f64(Cp, 2, dims, box, &mC);
     if (rc) return rc;
-    static int rpt = -1;
-    if (rpt < 0) rpt = env_int_("IGG_T2_RPT", 2);
     cudaStream_t st = (cudaStream_t)stream;
-    if (rpt == 4) rc = launch_t2<4>(mT, mC, p, st);
-    else rc = launch_t2<2>(mT, mC, p, st);
+    if (srb == 16 && rpt == 4) rc = launch_t2<16, 4>(mT, mC, p, st);
+    else if (srb == 16) rc = launch_t2<16, 2>(mT, mC, p, st);
+    else if (rpt == 4) rc = launch_t2<8, 4>(mT, mC, p, st);
+    else rc = launch_t2<8, 2>(mT, mC, p, st);
     if (rc) return rc;
     IGG_LAUNCH_CHECK();
     return 0;

@@ -38,17 +38,17 @@ namespace igg_t2 {
 constexpr int BW = 128;            // box width in doubles (1024 B per row)
 constexpr int BYO = BW - 4;        // output columns per work item
 constexpr int NPAIR = BW / 2;      // column pairs = consumer threads per row group
-constexpr int SRB = 16;            // rows per block
+// rows per block: template parameter S of the kernels (16: one CTA of 16 warps per SM; 8: half-size rings so that
+// two CTAs share an SM and one computes while the other sits in its per-block barrier); Geom.srb at run time
 constexpr int SNT = 4;             // T ring: b-1, b, b+1 in use + one in flight
 constexpr int SNC = 3;             // Cp ring: b-1, b in use + one in flight
 constexpr int SNM = 3;             // mid ring: b-1, b in use + the one step 1 of b+1 writes
-constexpr int BLK = SRB * BW;      // doubles per block
-constexpr int BLK_BYTES = BLK * 8; // 16384
+constexpr int blk_doubles(int srb) { return srb * BW; }          // doubles per block (16 rows: 16 KB)
 // The rings sit back to back (T, Cp, mid) with RING_PAD doubles of slack before the first and after the last
 // block: the left/right neighbour loads of box columns 0 and BW-1 are unconditional and may touch one element
 // outside a block.
 constexpr int RING_PAD = 16;
-constexpr int RING_DOUBLES = (SNT + SNC + SNM) * BLK;
+constexpr int ring_doubles(int srb) { return (SNT + SNC + SNM) * blk_doubles(srb); }
 
 #if defined(__CUDACC__)
 typedef double2 d2;
@@ -110,15 +110,17 @@ T2_HD double boundary_mid(const MidLines& ml, int x, int y, int nx, int ny, doub
 // ---- work items --------------------------------------------------------------------------------------
 struct Geom {
     int nx, ny;
-    int scx;        // output rows per strip, (scx + 4) % SRB == 0
+    int srb;        // rows per block (8 or 16)
+    int scx;        // output rows per strip, (scx + 4) % srb == 0
     int nti, ntj;   // strips, tile columns
     int frame_first;  // 1: items on the array edge come first (they push to the neighbours)
 };
 
-inline Geom make_geom(int nx, int ny, int scx, int frame_first) {
+inline Geom make_geom(int nx, int ny, int srb, int scx, int frame_first) {
     Geom g;
     g.nx = nx;
     g.ny = ny;
+    g.srb = srb;
     g.scx = scx;
     g.nti = (nx - 2 + scx - 1) / scx;
     g.ntj = (ny - 2) / BYO + 1;
@@ -164,13 +166,13 @@ T2_HD Item make_item(const Geom& g, int t) {
     it.rows_out = left < g.scx ? left : g.scx;
     it.xin0 = it.x0 - 2;
     it.yb = it.j * BYO - 2;
-    it.nbi = (it.rows_out + 4 + SRB - 1) / SRB;
+    it.nbi = (it.rows_out + 4 + g.srb - 1) / g.srb;
     return it;
 }
 
 // does every cell of the item's blocks lie in the updated region [1,nx-2] x [1,ny-2]?
 T2_HD bool item_is_inner(const Geom& g, const Item& it) {
-    return it.xin0 >= 1 && it.xin0 + it.nbi * SRB - 1 <= g.nx - 2 && it.yb >= 1 && it.yb + BW - 1 <= g.ny - 2;
+    return it.xin0 >= 1 && it.xin0 + it.nbi * g.srb - 1 <= g.nx - 2 && it.yb >= 1 && it.yb + BW - 1 <= g.ny - 2;
 }
 
 // ---- step 1: mid values of block b --------------------------------------------------------------------
@@ -178,7 +180,7 @@ T2_HD bool item_is_inner(const Geom& g, const Item& it) {
 // prevT / nextT: blocks b-1 / b+1 (any readable block when they do not exist: the rows that would need them
 // are never used).  xb = global row of the block's row 0.
 // The mid values are also returned (mA/mB, row r of the thread) for the optional step-(k+1) diagnostic.
-template <int RPT>
+template <int SRB, int RPT>
 T2_HD void step1_rows(const double* prevT, const double* curT, const double* nextT, const double* curC,
                       double* curM, int cp, int rg, int xb, int yb, int nx, int ny, const Phys& ph,
                       const MidLines& ml, bool inner, double (&oA)[RPT], double (&oB)[RPT]) {
@@ -239,7 +241,7 @@ T2_HD void step1_own_masks(int cp, int rg, int xb, int yb, int x_lo, int x_hi, i
 // Thread (cp, rg) owns the rows xb - 1 + rg*RPT + r.  prevM / prevC: mid and Cp of block b-1 (any readable
 // block for b == 0; those rows are masked).  [x_lo, x_hi]: the item's valid output rows (already clipped to
 // [1, nx-2]).  Returns the two values per row and the write masks (bit r = row r).
-template <int RPT>
+template <int SRB, int RPT>
 T2_HD void step2_rows(const double* prevM, const double* curM, const double* prevC, const double* curC, int cp,
                       int rg, int xb, int yb, int x_lo, int x_hi, int ny, const Phys& ph, double (&oA)[RPT],
                       double (&oB)[RPT], unsigned& wA, unsigned& wB) {

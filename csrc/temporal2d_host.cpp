@@ -18,9 +18,9 @@ using namespace igg_t2;
 
 namespace {
 
-// what cp.async.bulk.tensor does for a [SRB x BW] box at (x, y): out-of-range elements read as zero
-void load_box(const double* A, int nx, int ny, int x, int y, double* dst) {
-    for (int r = 0; r < SRB; ++r) {
+// what cp.async.bulk.tensor does for a [srb x BW] box at (x, y): out-of-range elements read as zero
+void load_box(const double* A, int nx, int ny, int x, int y, int srb, double* dst) {
+    for (int r = 0; r < srb; ++r) {
         const int gx = x + r;
         for (int c = 0; c < BW; ++c) {
             const int gy = y + c;
@@ -29,11 +29,12 @@ void load_box(const double* A, int nx, int ny, int x, int y, double* dst) {
     }
 }
 
-template <int RPT>
+template <int SRB, int RPT>
 void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const Phys& ph1, const Phys& ph2,
              int workers, const MidLines& ml, double* diag) {
     double d1max = -HUGE_VAL, d1sum = 0.0, d2max = -HUGE_VAL, d2sum = 0.0;
     constexpr int NRG = SRB / RPT;
+    constexpr int BLK = blk_doubles(SRB), RING_DOUBLES = ring_doubles(SRB);
     const int nitems = num_items(g);
     // 16-byte aligned rings, poisoned so that a read of a slot that was never filled shows up
     // same layout as the kernel's shared memory: pad | T ring | Cp ring | mid ring | pad
@@ -53,12 +54,12 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
             const Item it = make_item(g, w + k * workers);
             const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;
             const bool inner = item_is_inner(g, it);
-            load_box(T, g.nx, g.ny, it.xin0, it.yb, ringT + (tq % SNT) * BLK);
+            load_box(T, g.nx, g.ny, it.xin0, it.yb, SRB, ringT + (tq % SNT) * BLK);
             for (int b = 0; b < it.nbi; ++b) {
                 const unsigned qb = tq + b, qc = cq + b, qm = mq + b;
                 if (b + 1 < it.nbi)
-                    load_box(T, g.nx, g.ny, it.xin0 + (b + 1) * SRB, it.yb, ringT + ((qb + 1) % SNT) * BLK);
-                load_box(Cp, g.nx, g.ny, it.xin0 + b * SRB, it.yb, ringC + (qc % SNC) * BLK);
+                    load_box(T, g.nx, g.ny, it.xin0 + (b + 1) * SRB, it.yb, SRB, ringT + ((qb + 1) % SNT) * BLK);
+                load_box(Cp, g.nx, g.ny, it.xin0 + b * SRB, it.yb, SRB, ringC + (qc % SNC) * BLK);
                 const double* curT = ringT + (qb % SNT) * BLK;
                 const double* prevT = b > 0 ? ringT + ((qb + SNT - 1) % SNT) * BLK : curT;
                 const double* nextT = b + 1 < it.nbi ? ringT + ((qb + 1) % SNT) * BLK : curT;
@@ -71,7 +72,7 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
                     for (int cp = 0; cp < NPAIR; ++cp) {
                         double mA[RPT], mB[RPT];
                         unsigned wA, wB;
-                        step1_rows<RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, g.nx, g.ny, ph1, ml, inner, mA, mB);
+                        step1_rows<SRB, RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, g.nx, g.ny, ph1, ml, inner, mA, mB);
                         step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, g.ny, wA, wB);
                         for (int r = 0; r < RPT; ++r) {
                             if ((wA >> r) & 1u) { d1max = mA[r] > d1max ? mA[r] : d1max; d1sum += mA[r]; }
@@ -83,7 +84,7 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
                     for (int cp = 0; cp < NPAIR; ++cp) {
                         double oA[RPT], oB[RPT];
                         unsigned wA, wB;
-                        step2_rows<RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, g.ny, ph2, oA, oB,
+                        step2_rows<SRB, RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, g.ny, ph2, oA, oB,
                                         wA, wB);
                         const int y = it.yb + 2 * cp;
                         for (int r = 0; r < RPT; ++r) {
@@ -117,13 +118,14 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
 }  // namespace
 
 extern "C" int igg_cpu_temporal2d_emulate(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
-                                          double dt, double _dx, double _dy, int scx, int rpt, int workers,
-                                          const double* mid_lines, int side_mask, const double* phys2,
-                                          double* diag_out) {
+                                          double dt, double _dx, double _dy, int srb, int scx, int rpt,
+                                          int workers, const double* mid_lines, int side_mask,
+                                          const double* phys2, double* diag_out) {
     if (!T || !T2 || !Cp || nx < 3 || ny < 4 || (ny & 1)) return IGG_ERR_INVALID;
-    if (scx < SRB - 4 || (scx + 4) % SRB || workers < 1 || (rpt != 2 && rpt != 4)) return IGG_ERR_INVALID;
+    if (srb != 8 && srb != 16) return IGG_ERR_INVALID;
+    if (scx < srb - 4 || (scx + 4) % srb || workers < 1 || (rpt != 2 && rpt != 4)) return IGG_ERR_INVALID;
     if (side_mask && !mid_lines) return IGG_ERR_INVALID;
-    const Geom g = make_geom(nx, ny, scx, side_mask ? 1 : 0);
+    const Geom g = make_geom(nx, ny, srb, scx, side_mask ? 1 : 0);
     Phys ph;
     ph.lam = lam;
     ph.dt = dt;
@@ -141,8 +143,10 @@ extern "C" int igg_cpu_temporal2d_emulate(const double* T, double* T2, const dou
         ph2._dx = phys2[2];
         ph2._dy = phys2[3];
     }
-    if (rpt == 4) emulate<4>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
-    else emulate<2>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
+    if (srb == 16 && rpt == 4) emulate<16, 4>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
+    else if (srb == 16) emulate<16, 2>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
+    else if (rpt == 4) emulate<8, 4>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
+    else emulate<8, 2>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
     return 0;
 }
 

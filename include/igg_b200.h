@@ -168,11 +168,11 @@ int igg_diffusion2d_midlines(const double* T, const double* Cp, int nx, int ny, 
 /* output rows per work item of igg_diffusion2d_step2 (IGG_T2_ROWS, default 252) */
 int igg_temporal2d_default_rows(void);
 /* Host emulation of igg_diffusion2d_step2 that executes the kernel's own index code (csrc/temporal2d_core.h)
- * thread by thread: `workers` plays gridDim.x, `rpt` the rows per thread (2 or 4), `scx` the rows per work item
- * ((scx + 4) % 16 == 0).  `mid_lines`: this rank's mid-line buffer or NULL; `side_mask` bit s = a neighbour
+ * thread by thread: `workers` plays gridDim.x, `srb` the rows per block (8 or 16; IGG_T2_SRB), `rpt` the rows per
+ * thread (2 or 4; IGG_T2_RPT), `scx` the rows per work item ((scx + 4) % srb == 0; IGG_T2_ROWS).  `mid_lines`: this rank's mid-line buffer or NULL; `side_mask` bit s = a neighbour
  * exists on side s.  igg_cpu_temporal2d_midlines fills the neighbours' buffers (`peer_mid[s]`, NULL = none). */
 int igg_cpu_temporal2d_emulate(const double* T, double* T2, const double* Cp, int nx, int ny, double lam,
-                               double dt, double _dx, double _dy, int scx, int rpt, int workers,
+                               double dt, double _dx, double _dy, int srb, int scx, int rpt, int workers,
                                const double* mid_lines, int side_mask, const double* phys2 /* step k+2, or NULL */,
                                double* diag_out /* {max1, sum1, max2, sum2} or NULL */);
 int igg_cpu_temporal2d_midlines(const double* T, const double* Cp, int nx, int ny, double lam, double dt,

@@ -113,7 +113,7 @@ def _declare(lib) -> None:
                                              C.POINTER(Mid2D), vp], i),
         "igg_diffusion2d_midlines": ([vp, vp, i, i, d, d, d, d, vp, C.POINTER(Push2D), C.POINTER(Mid2D), vp], i),
         "igg_temporal2d_default_rows": ([], i),
-        "igg_cpu_temporal2d_emulate": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, vp, i, vp, vp], i),
+        "igg_cpu_temporal2d_emulate": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, i, vp, i, vp, vp], i),
         "igg_cpu_temporal2d_midlines": ([vp, vp, i, i, d, d, d, d, C.POINTER(vp)], i),
     }
     for name, (argtypes, restype) in sig.items():
@@ -507,7 +507,7 @@ def temporal2d_default_rows() -> int:
 def cpu_temporal2d_emulate(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam, dt, _dx, _dy, scx: int = 252,
                            rpt: int = 2, workers: int = 148, mid_lines: Optional[torch.Tensor] = None,
                            side_mask: int = 0, phys2: Optional[Sequence[float]] = None,
-                           diag_out: Optional[torch.Tensor] = None) -> None:
+                           diag_out: Optional[torch.Tensor] = None, srb: int = 16) -> None:
     """Run the index code of the two-steps-per-pass CUDA kernel on the host, thread by thread
     (``igg_cpu_temporal2d_emulate``): ``T2 <- step(step(T))`` on the cells that kernel writes."""
     lib = require()
@@ -521,7 +521,7 @@ def cpu_temporal2d_emulate(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, 
     if diag_out is not None and (diag_out.is_cuda or diag_out.dtype != torch.float64 or diag_out.numel() < 4):
         raise TypeError("diag_out must be a CPU float64 tensor of 4 elements")
     _check(lib.igg_cpu_temporal2d_emulate(T.data_ptr(), T2.data_ptr(), Cp.data_ptr(), nx, ny, lam, dt, _dx, _dy,
-                                          scx, rpt, workers,
+                                          srb, scx, rpt, workers,
                                           mid_lines.data_ptr() if mid_lines is not None else None, side_mask,
                                           C.cast(p2, C.c_void_p) if p2 is not None else None,
                                           diag_out.data_ptr() if diag_out is not None else None))

@@ -22,4 +22,5 @@ export IGG_B200_TRANSPORT=${IGG_B200_TRANSPORT:-peer}
 #   IGG_E2E_SPIN   1  = step_controlled waits by polling an event (0: cudaStreamSynchronize)
 #   IGG_T2_RPT     2  = two-steps-per-pass kernel (experimental): rows per consumer thread (2: 16 warps, 4: 8 warps)
 #   IGG_T2_ROWS    252 = its output rows per work item ((rows + 4) % 16 == 0)
+#   IGG_T2_SRB     16 = its rows per block (8: half-size rings, two CTAs per SM)
 echo "ENV setup done (transport: $IGG_B200_TRANSPORT)"

@@ -7,10 +7,12 @@ NX=${1:-16384}; NY=${2:-16384}; STEPS=${3:-40}
 OUT="$REPO/gpurun_out/temporal_sweep.txt"
 mkdir -p "$REPO/gpurun_out"
 : > "$OUT"
-for rpt in 2 4; do
+for srb in 16 8; do
+ for rpt in 2 4; do
   for rows in 124 252 508; do
-    echo "== IGG_T2_RPT=$rpt IGG_T2_ROWS=$rows" | tee -a "$OUT"
-    IGG_T2_RPT=$rpt IGG_T2_ROWS=$rows timeout 300 python "$REPO/scripts/check_temporal.py" \
+    echo "== IGG_T2_SRB=$srb IGG_T2_RPT=$rpt IGG_T2_ROWS=$rows" | tee -a "$OUT"
+    IGG_T2_SRB=$srb IGG_T2_RPT=$rpt IGG_T2_ROWS=$rows timeout 300 python "$REPO/scripts/check_temporal.py" \
         --nx "$NX" --ny "$NY" --steps "$STEPS" --timing-only 2>&1 | grep -E "ms/step|MISMATCH|rror" | tee -a "$OUT"
   done
+ done
 done

@@ -35,13 +35,14 @@ def _two_steps(T, Cp):
 @pytest.mark.parametrize("shape", [(3, 4), (4, 4), (5, 6), (17, 130), (40, 126), (41, 128), (64, 250),
                                    (130, 258), (300, 380)])
 @pytest.mark.parametrize("rpt", [2, 4])
-def test_emulated_kernel_equals_two_steps(shape, rpt):
+@pytest.mark.parametrize("srb", [8, 16])
+def test_emulated_kernel_equals_two_steps(shape, rpt, srb):
     T, Cp = _fields(*shape)
     want = _two_steps(T, Cp)
-    for scx, workers in [(12, 1), (12, 5), (28, 3), (252, 148)]:
+    for scx, workers in [(12, 1), (12, 5), (28, 3), (252, 148)] + ([(4, 2), (20, 296)] if srb == 8 else []):
         T2 = T.clone()
-        native.cpu_temporal2d_emulate(T2, T, Cp, *PH, scx=scx, rpt=rpt, workers=workers)
-        assert torch.equal(T2, want), (shape, rpt, scx, workers, float((T2 - want).abs().max()))
+        native.cpu_temporal2d_emulate(T2, T, Cp, *PH, scx=scx, rpt=rpt, workers=workers, srb=srb)
+        assert torch.equal(T2, want), (shape, rpt, srb, scx, workers, float((T2 - want).abs().max()))
 
 
 def test_bench_like_geometry():
@@ -50,6 +51,9 @@ def test_bench_like_geometry():
     want = _two_steps(T, Cp)
     T2 = T.clone()
     native.cpu_temporal2d_emulate(T2, T, Cp, *PH, scx=native.temporal2d_default_rows(), rpt=2, workers=148)
+    assert torch.equal(T2, want)
+    T2 = T.clone()                       # 8-row blocks: two CTAs per SM
+    native.cpu_temporal2d_emulate(T2, T, Cp, *PH, scx=native.temporal2d_default_rows(), rpt=2, workers=296, srb=8)
     assert torch.equal(T2, want)
 
 
@@ -81,11 +85,12 @@ def _side_neighbors(vg, r):
 @pytest.mark.parametrize("dims,periods", [((2, 1), (0, 0)), ((1, 2), (0, 0)), ((2, 2), (0, 0)), ((3, 2), (0, 0)),
                                           ((2, 2), (1, 1)), ((1, 1), (1, 1)), ((3, 1), (1, 0))])
 @pytest.mark.parametrize("local", [(20, 24), (37, 130)])
-def test_virtual_ranks_with_mid_lines(dims, periods, local):
-    _run_virtual(dims, periods, local, scx=12, rpt=2, workers=3)
+@pytest.mark.parametrize("srb", [8, 16])
+def test_virtual_ranks_with_mid_lines(dims, periods, local, srb):
+    _run_virtual(dims, periods, local, scx=12, rpt=2, workers=3, srb=srb)
 
 
-def _run_virtual(dims, periods, local, scx, rpt, workers):
+def _run_virtual(dims, periods, local, scx, rpt, workers, srb=16):
     """Per pass: every rank sends its step-(k+1) edge lines, runs the two-step pass, then the step-(k+2) halo
     exchange happens (the in-kernel push of the real kernel).  Result == two (step + update_halo) rounds."""
     nx, ny = local
@@ -119,7 +124,7 @@ def _run_virtual(dims, periods, local, scx, rpt, workers):
             sides = _side_neighbors(vg, r)
             mask = sum(1 << k for k, s in enumerate(sides) if s != PROC_NULL)
             native.cpu_temporal2d_emulate(nxt[r], cur[r], Cp[r], *PH, scx=scx, rpt=rpt, workers=workers,
-                                          mid_lines=mids[r], side_mask=mask)
+                                          mid_lines=mids[r], side_mask=mask, srb=srb)
         vg.update_halo(nxt)
         cur = nxt
     for r in range(n):
