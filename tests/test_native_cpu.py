@@ -33,15 +33,28 @@ def test_cpu_step_bit_exact_vs_torch():
 
 
 def test_cpu_run_matches_oracle():
-    T_ref, dt = ref.oracle_2d(62, 48, 25, "perf")
+    """25 native steps == 25 PyTorch steps from the SAME initial field, bit for bit.
+
+    (The initial condition is evaluated once on purpose: this test has failed intermittently -- about one full-suite
+    run in five, never in isolation -- when the oracle and the native run each evaluated their own
+    ``exp(-x^2-y^2)``; if the stepping itself ever differs the message below says so.)"""
     dx, dy = 10.0 / 62, 10.0 / 48
+    dt = ref.time_step(dx, dy, 1.0, 1.0)
     xs = torch.arange(62, dtype=torch.float64) * dx
     ys = torch.arange(48, dtype=torch.float64) * dy
-    T = ref.gaussian_ic(xs, ys, dx, dy, 10.0, 10.0)
-    T2 = T.clone()
-    Cp = torch.ones_like(T)
+    T0 = ref.gaussian_ic(xs, ys, dx, dy, 10.0, 10.0)
+    Cp = torch.ones_like(T0)
+    A, B = T0.clone(), T0.clone()
+    for _ in range(25):
+        ref.perf_step(B, A, Cp, 1.0, dt, 1.0 / dx, 1.0 / dy)
+        A, B = B, A
+    T, T2 = T0.clone(), T0.clone()
     native.cpu_diffusion2d_run(T, T2, Cp, 1.0, dt, 1.0 / dx, 1.0 / dy, 25)
-    assert torch.equal(T, T_ref)
+    assert torch.equal(T, A), (f"native vs torch stepping from the same field: {int((T != A).sum())} cells differ, "
+                               f"max {float((T - A).abs().max()):.3e}; threads = {torch.get_num_threads()}")
+    # the packaged oracle (its own evaluation of the initial condition) agrees to rounding in any case
+    T_ref, dt_ref = ref.oracle_2d(62, 48, 25, "perf")
+    assert dt_ref == dt and float((T - T_ref).abs().max()) < 1e-15
 
 
 def test_cpu_kp_kernels_match_reference():
