@@ -35,7 +35,9 @@ def make_solver(cfg: DiffusionConfig, mode: str):
         return Diffusion2DHost(cfg.nx, cfg.ny, lx=cfg.lx, ly=cfg.ly, lam=cfg.lam, Cp0=cfg.Cp0,
                                mode="hide" if mode == "hide" else "plain", b_width=cfg.b_width[:2])
     from ..parallel.comm import spans_nodes
-    if spans_nodes() and mode != "plain":
+    if mode == "hide" and (cfg.transport in ("nccl", "host") or spans_nodes()):
+        mode = "hide_exchange"      # overlap with a library exchange instead of in-kernel peer stores
+    if spans_nodes() and mode not in ("plain", "hide_exchange"):
         log0(f"ranks span several nodes: mode '{mode}' needs peer memory, falling back to plain + NCCL")
         mode = "plain"
     return Diffusion2D(cfg.nx, cfg.ny, lx=cfg.lx, ly=cfg.ly, lam=cfg.lam, Cp0=cfg.Cp0, mode=mode, variant=cfg.kernel,

@@ -10,6 +10,11 @@ offers three ways to advance, all producing the same field:
            (``scripts/diffusion_2D_perf_hide.jl:94-101``): boundary frame of width ``b_width`` on a
            high-priority stream (pushing edges as it goes), interior on a low-priority stream,
            join, swap.
+``hide_exchange``  the same structure spelled the way the reference comments it (variant (3),
+           ``scripts/diffusion_2D_perf_hide.jl:94-101``): boundary frame kernel, then ``update_halo(T2)`` over the
+           chosen transport on the high-priority stream WHILE the interior kernel runs on the low-priority one,
+           join, swap.  This is the overlap form for transports without peer stores (``nccl`` across nodes, ``host``);
+           built from GPU-tested parts, the combination itself has not run on hardware yet.
 ``persistent``  for small local grids: ``step(n)`` is ONE cooperative launch that runs all ``n`` steps with
            in-kernel grid barriers and the same in-kernel halo pushes (no per-step launch latency).
 ``resident``  for grids that fit in the shared memory of one thread-block cluster (up to ~256 x 256): the
@@ -50,8 +55,8 @@ class Diffusion2D:
             raise RuntimeError("Diffusion2D runs on CUDA devices; use models.diffusion2d_ap on CPU")
         if (nx, ny) != tuple(g.nxyz[:2]):
             raise ValueError("nx, ny must be the local sizes given to init_global_grid")
-        if mode not in ("fused", "hide", "plain", "persistent", "resident", "temporal"):
-            raise ValueError("mode must be fused | hide | plain | persistent | resident | temporal")
+        if mode not in ("fused", "hide", "hide_exchange", "plain", "persistent", "resident", "temporal"):
+            raise ValueError("mode must be fused | hide | hide_exchange | plain | persistent | resident | temporal")
         if mode == "temporal" and variant != "tma":
             raise ValueError("mode='temporal' is a TMA kernel (variant='tma', even ny)")
         native.require()
@@ -98,7 +103,7 @@ class Diffusion2D:
         self.steps_done = 0
         # streams for the hide structure (reference perf_hide.jl:63-68: HIGH / LOW priority queues)
         self._s_hi = self._s_lo = None
-        if mode == "hide":
+        if mode in ("hide", "hide_exchange"):
             self._s_hi = torch.cuda.Stream(device=dev, priority=-1)      # -1 = high, 0 = default
             self._s_lo = torch.cuda.Stream(device=dev, priority=0)
             self._ev_hi = torch.cuda.Event()
@@ -257,6 +262,22 @@ class Diffusion2D:
                 main.wait_event(self._ev_hi)
                 main.wait_event(self._ev_lo)
                 self.T, self.T2 = self.T2, self.T
+            elif self.mode == "hide_exchange":
+                main = torch.cuda.current_stream()
+                self._ev_main.record(main)
+                self._s_hi.wait_event(self._ev_main)
+                self._s_lo.wait_event(self._ev_main)
+                with torch.cuda.stream(self._s_hi):
+                    self._kernel(1, None, dev_params)                       # boundary frame
+                    if self.g.nprocs > 1 or any(self.g.periods):
+                        update_halo(self.T2, transport=self.transport)      # exchange of the NEW field ...
+                    self._ev_hi.record(self._s_hi)
+                with torch.cuda.stream(self._s_lo):
+                    self._kernel(2, None, dev_params)                       # ... while the interior is computed
+                    self._ev_lo.record(self._s_lo)
+                main.wait_event(self._ev_hi)
+                main.wait_event(self._ev_lo)
+                self.T, self.T2 = self.T2, self.T
             else:
                 self._kernel(0, None, dev_params, diag_out)
                 self.T, self.T2 = self.T2, self.T
@@ -327,7 +348,7 @@ class Diffusion2D:
         """Native kernel launches per ``step()`` (for launch accounting)."""
         if self.mode == "fused":
             return 1
-        if self.mode == "hide":
+        if self.mode in ("hide", "hide_exchange"):
             return 2
         return 1      # "persistent": one launch per step() call, however many steps
 
