@@ -11,7 +11,7 @@ echo "== stage 1: numerics (kernel alone, solver with self-neighbour, controlled
 timeout 600 python scripts/check_temporal.py --skip-timing > $OUT/t2_check.log 2>&1
 rc=$?; echo "check_temporal rc=$rc" | tee -a $OUT/t2_summary.txt; tail -n 25 $OUT/t2_check.log
 echo "== stage 2: staged pytest tier" | tee -a $OUT/t2_summary.txt
-timeout 900 python -m pytest tests -m temporal_gpu -q > $OUT/t2_pytest.log 2>&1
+timeout 900 python -m pytest tests -m "temporal_gpu or staged_gpu" -q > $OUT/t2_pytest.log 2>&1
 echo "pytest rc=$?" | tee -a $OUT/t2_summary.txt; tail -n 5 $OUT/t2_pytest.log | tee -a $OUT/t2_summary.txt
 if [ $rc -eq 0 ]; then
   echo "== stage 3: timing at 16384^2, fused vs temporal" | tee -a $OUT/t2_summary.txt
