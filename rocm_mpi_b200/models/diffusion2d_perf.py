@@ -63,6 +63,23 @@ def run_timed(s, nt: int, warmup: int) -> float:
     return wtime
 
 
+def _run_chunked(s, nt: int, warmup: int, every: int, directory: str):
+    """Time loop cut at checkpoint steps: chunks end where ``steps_done`` is a multiple of ``every``; only the
+    first chunk has untimed warm-up steps.  Returns ``(timed seconds, untimed steps)``."""
+    wtime, untimed, first = 0.0, 0, True
+    while s.steps_done < nt:
+        n = nt - s.steps_done
+        if every > 0:
+            n = min(n, every - s.steps_done % every)
+        w = min(warmup, max(n - 1, 0)) if first else 0
+        wtime += run_timed(s, n, w)
+        untimed += w
+        first = False
+        if every > 0 and s.steps_done % every == 0:
+            s.save(directory)
+    return wtime, untimed
+
+
 def diffusion2D_perf(cfg: DiffusionConfig = None, mode: str = None, variant_name: str = "perf",
                      finalize: bool = True) -> RunResult:
     cfg = cfg or DiffusionConfig(nx=16384, ny=16384, nt=110, do_vis=False)
@@ -72,11 +89,22 @@ def diffusion2D_perf(cfg: DiffusionConfig = None, mode: str = None, variant_name
     n0 = native.launch_count()
     s = make_solver(cfg, mode)
     nt, warm = int(cfg.nt), min(int(cfg.warmup), max(int(cfg.nt) - 1, 0))
+    if cfg.resume:
+        from ..utils.checkpoint import latest_checkpoint
+        path = latest_checkpoint(cfg.ckpt_dir)
+        if path is not None:
+            step = s.load(path)                       # collective
+            log0(f"Resuming from {path} (step {step})")
+    start_step = s.steps_done
     log0("Starting the time loop ...", end="")
-    wtime = run_timed(s, nt, warm)
+    if cfg.ckpt_every > 0 or s.steps_done > 0:
+        wtime, warm = _run_chunked(s, nt, warm, int(cfg.ckpt_every), cfg.ckpt_dir)
+    else:
+        wtime = run_timed(s, nt, warm)
     log0("done")
+    steps_here = nt - start_step                     # fewer than nt after a resume
     A = a_eff((cfg.nx, cfg.ny))                      # reference scripts/diffusion_2D_perf.jl:55
-    wtime_it = wtime / max(nt - warm, 1)             # :56
+    wtime_it = wtime / max(steps_here - warm, 1)     # :56
     T_eff = A / wtime_it                             # :57
     log0("Executed %d steps in = %1.3e sec (@ T_eff = %1.2f GB/s) " % (nt, wtime, float("%.3g" % T_eff)))
     res = RunResult(variant_name, su.me, su.nprocs, su.dims, nt, wtime=wtime, t_eff=T_eff, T_local=s.T,

@@ -352,6 +352,27 @@ class Diffusion2D:
             return 2
         return 1      # "persistent": one launch per step() call, however many steps
 
+    # -- checkpoint / resume (the reference persists only the final PNG) -------------------
+    def save(self, directory: str) -> str:
+        """Collective: write ``T`` and ``Cp`` (halo included) of every rank; returns the checkpoint path.
+        Call between ``finish()`` and the next ``begin()`` (pushes of the last step must have landed)."""
+        from ..utils.checkpoint import save_checkpoint
+        if self._running:
+            self.finish()
+        return save_checkpoint(directory, self.steps_done, T=self.T, Cp=self.Cp)
+
+    def load(self, path: str) -> int:
+        """Collective: restore the fields and the step counter from ``path``; returns the step."""
+        from ..utils.checkpoint import load_checkpoint
+        if self._running:
+            self.finish()
+        step, f = load_checkpoint(path, device=self.T.device)
+        self.T.copy_(f["T"])
+        self.T2.copy_(f["T"])
+        self.Cp.copy_(f["Cp"])
+        self.steps_done = step
+        return step
+
     def max_sum(self) -> Tuple[float, float]:
         out = native.reduce_max_sum(self.T.view(-1))
         v = out.cpu()

@@ -76,6 +76,22 @@ class Diffusion2DHost:
                     update_halo(self.T)
             self.steps_done += 1
 
+    # -- checkpoint / resume (the reference persists only the final PNG) -------------------
+    def save(self, directory: str) -> str:
+        """Collective: write ``T`` and ``Cp`` (halo included) of every rank; returns the checkpoint path."""
+        from ..utils.checkpoint import save_checkpoint
+        return save_checkpoint(directory, self.steps_done, T=self.T, Cp=self.Cp)
+
+    def load(self, path: str) -> int:
+        """Collective: restore the fields and the step counter from ``path``; returns the step."""
+        from ..utils.checkpoint import load_checkpoint
+        step, f = load_checkpoint(path)
+        self.T.copy_(f["T"])
+        self.T2.copy_(f["T"])
+        self.Cp.copy_(f["Cp"])
+        self.steps_done = step
+        return step
+
     def max_sum(self) -> Tuple[float, float]:
         inner = self.T[1:-1, 1:-1]
         return float(inner.max()), float(inner.sum())

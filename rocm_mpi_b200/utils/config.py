@@ -51,6 +51,10 @@ class DiffusionConfig:
     kernel: str = "tma"                          # tma | direct  (stencil kernel flavour)
     fused: bool = True                           # fuse the halo push into the stencil kernel
     device_type: str = "auto"
+    # checkpoint / resume (none in the reference)
+    ckpt_every: int = 0                          # write a checkpoint every N steps (0 = never)
+    ckpt_dir: str = "output/ckpt"
+    resume: bool = False                         # start from the latest checkpoint in ckpt_dir, if there is one
     # output
     do_vis: bool = True
     outdir: str = "output"

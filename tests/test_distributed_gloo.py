@@ -53,6 +53,11 @@ def test_per_rank_before_after_pictures(tmp_path):
     assert any("max |halo - neighbour's edge| across x seams = 0.0e+00" in o for o in outs)
 
 
+def test_checkpoint_and_resume_through_the_perf_app(tmp_path):
+    outs = run_workers("ckpt_gloo.py", 4, (str(tmp_path),), timeout=300)
+    assert all("ok" in o for o in outs)
+
+
 def test_ring_smoke_test_over_gloo():
     outs = run_workers("ring_gloo.py", 4)
     assert all("ok" in o for o in outs)
