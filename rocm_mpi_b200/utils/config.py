@@ -67,15 +67,33 @@ class DiffusionConfig:
         self.b_width = bw + (bw[-1],) * (3 - len(bw))
 
 
+def _to_bool(s: str) -> bool:
+    return s.strip().lower() not in ("0", "false", "no", "off", "")
+
+
+def _env_default(name: str, v):
+    """``IGG_B200_<FIELD>`` overrides a field's default (the command line still wins)."""
+    env = os.environ.get("IGG_B200_" + name.upper())
+    if env is None or env == "":
+        return v
+    if name == "b_width":
+        return [int(x) for x in env.replace(",", " ").split()]
+    if isinstance(v, bool):
+        return _to_bool(env)
+    if v is None:
+        return env
+    return type(v)(env)
+
+
 def add_config_args(p: argparse.ArgumentParser, defaults: Optional[DiffusionConfig] = None) -> None:
     d = defaults or DiffusionConfig()
     for f in fields(DiffusionConfig):
-        v = getattr(d, f.name)
+        v = _env_default(f.name, getattr(d, f.name))
         flag = "--" + f.name.replace("_", "-")
         if f.name == "b_width":
             p.add_argument(flag, type=int, nargs="+", default=list(v))
         elif isinstance(v, bool):
-            p.add_argument(flag, type=lambda s: s.lower() not in ("0", "false", "no"), default=v)
+            p.add_argument(flag, type=_to_bool, default=v)
         elif v is None:
             p.add_argument(flag, type=str, default=None)
         else:

@@ -64,3 +64,19 @@ def test_config_cli_roundtrip(monkeypatch):
     assert DiffusionConfig().transport == "host"
     monkeypatch.setenv("X_FLAG", "0")
     assert env_flag("X_FLAG", True) is False and env_flag("X_MISSING", True) is True
+
+
+def test_config_env_overrides_defaults_and_cli_wins(monkeypatch):
+    """IGG_B200_<FIELD> environment variables replace the script constants of the reference (SURVEY.md section 5,
+    "Config / flags"); explicit command-line flags take precedence."""
+    import argparse
+    from rocm_mpi_b200.utils.config import DiffusionConfig, add_config_args, config_from_args
+    monkeypatch.setenv("IGG_B200_NX", "300")
+    monkeypatch.setenv("IGG_B200_DO_VIS", "0")
+    monkeypatch.setenv("IGG_B200_B_WIDTH", "8,2")
+    monkeypatch.setenv("IGG_B200_LAM", "2.5")
+    monkeypatch.setenv("IGG_B200_TRANSPORT", "nccl")
+    p = argparse.ArgumentParser()
+    add_config_args(p, DiffusionConfig(nx=128, ny=64))
+    c = config_from_args(p.parse_args(["--ny", "70", "--lam", "3.0"]))
+    assert (c.nx, c.ny, c.do_vis, c.b_width, c.lam, c.transport) == (300, 70, False, (8, 2, 2), 3.0, "nccl")
