@@ -345,6 +345,7 @@ class PushPlan:
             self._desc[A.data_ptr()] = self._build(A)
         self._active = False
         self._mid: Optional[native.Mid2D] = None
+        self._desc2: Optional[Dict[int, object]] = None      # built by mid_lines()
 
     def mid_lines(self) -> "native.Mid2D":
         """Collective on first use: the mid-line buffers and flags of the two-steps-per-pass kernel
@@ -410,6 +411,8 @@ class PushPlan:
             raise RuntimeError("PushPlan.begin() must be called before the time loop")
         if not self.fab.neighbors:
             return None
+        if two_step and self._desc2 is None:
+            raise RuntimeError("call PushPlan.mid_lines() (collective) before asking for two-step descriptors")
         self.epoch += 1
         d = (self._desc2 if two_step else self._desc)[dst.data_ptr()]
         d.epoch = self.epoch
