@@ -44,17 +44,28 @@ def make_solver(cfg: DiffusionConfig, mode: str):
                        b_width=cfg.b_width[:2], transport=cfg.transport)
 
 
-def run_timed(s, nt: int, warmup: int) -> float:
+def _steps(s, n: int, tracer, per_step: bool) -> None:
+    if tracer is None or not per_step:
+        s.step(n)
+        return
+    for _ in range(n):                 # one span per step (slower than the native loop: tracing only)
+        with tracer.span(f"step {s.steps_done}", "steps"):
+            s.step(1)
+
+
+def run_timed(s, nt: int, warmup: int, tracer=None, trace_steps: bool = False) -> float:
     """The reference's time loop: ``tic()`` once ``warmup`` iterations are done, ``toc()`` at the end."""
+    import contextlib
+    span = tracer.span if tracer is not None else (lambda *a, **k: contextlib.nullcontext())
     s.begin()
     gc_was = gc.isenabled()
     gc.disable()                       # reference scripts/diffusion_2D_perf_hide.jl:73 (GC.enable(false))
     try:
-        with nvtx_range("warmup"):
-            s.step(warmup)
+        with nvtx_range("warmup"), span("warmup"):
+            _steps(s, warmup, tracer, trace_steps)
         tic()
-        with nvtx_range("timed_loop"):
-            s.step(nt - warmup)
+        with nvtx_range("timed_loop"), span("timed_loop"):
+            _steps(s, nt - warmup, tracer, trace_steps)
         wtime = toc()
     finally:
         if gc_was:
@@ -63,7 +74,7 @@ def run_timed(s, nt: int, warmup: int) -> float:
     return wtime
 
 
-def _run_chunked(s, nt: int, warmup: int, every: int, directory: str):
+def _run_chunked(s, nt: int, warmup: int, every: int, directory: str, tracer=None, trace_steps: bool = False):
     """Time loop cut at checkpoint steps: chunks end where ``steps_done`` is a multiple of ``every``; only the
     first chunk has untimed warm-up steps.  Returns ``(timed seconds, untimed steps)``."""
     wtime, untimed, first = 0.0, 0, True
@@ -72,7 +83,7 @@ def _run_chunked(s, nt: int, warmup: int, every: int, directory: str):
         if every > 0:
             n = min(n, every - s.steps_done % every)
         w = min(warmup, max(n - 1, 0)) if first else 0
-        wtime += run_timed(s, n, w)
+        wtime += run_timed(s, n, w, tracer, trace_steps)
         untimed += w
         first = False
         if every > 0 and s.steps_done % every == 0:
@@ -96,12 +107,18 @@ def diffusion2D_perf(cfg: DiffusionConfig = None, mode: str = None, variant_name
             step = s.load(path)                       # collective
             log0(f"Resuming from {path} (step {step})")
     start_step = s.steps_done
+    tracer = None
+    if cfg.trace:
+        from ..utils.profiling import Tracer
+        tracer = Tracer(rank=su.me)
     log0("Starting the time loop ...", end="")
     if cfg.ckpt_every > 0 or s.steps_done > 0:
-        wtime, warm = _run_chunked(s, nt, warm, int(cfg.ckpt_every), cfg.ckpt_dir)
+        wtime, warm = _run_chunked(s, nt, warm, int(cfg.ckpt_every), cfg.ckpt_dir, tracer, cfg.trace_steps)
     else:
-        wtime = run_timed(s, nt, warm)
+        wtime = run_timed(s, nt, warm, tracer, cfg.trace_steps)
     log0("done")
+    if tracer is not None:
+        tracer.dump(f"{cfg.trace}.rank{su.me}.json")
     steps_here = nt - start_step                     # fewer than nt after a resume
     A = a_eff((cfg.nx, cfg.ny))                      # reference scripts/diffusion_2D_perf.jl:55
     wtime_it = wtime / max(steps_here - warm, 1)     # :56

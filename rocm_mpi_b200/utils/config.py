@@ -55,6 +55,9 @@ class DiffusionConfig:
     ckpt_every: int = 0                          # write a checkpoint every N steps (0 = never)
     ckpt_dir: str = "output/ckpt"
     resume: bool = False                         # start from the latest checkpoint in ckpt_dir, if there is one
+    # timeline (Chrome / Perfetto trace, one file per rank: <trace>.rank<r>.json); trace_steps adds one span per step
+    trace: Optional[str] = None
+    trace_steps: bool = False
     # output
     do_vis: bool = True
     outdir: str = "output"

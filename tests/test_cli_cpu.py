@@ -52,3 +52,15 @@ def test_3d_app_runs_on_cpu(tmp_path):
     out = _run("rocm_mpi_b200.models.diffusion3d", "--nx", "12", "--ny", "10", "--nz", "9", "--nt", "5",
                "--device-type", "cpu", "--outdir", str(tmp_path), cwd=str(tmp_path))
     assert "Global grid: 12x10x9" in out
+
+
+def test_trace_flag_writes_a_chrome_trace(tmp_path):
+    import json
+    _run("rocm_mpi_b200.models.diffusion2d_perf", "--nx", "34", "--ny", "30", "--nt", "12", "--warmup", "3",
+         "--device-type", "cpu", "--do-vis", "false", "--trace", str(tmp_path / "tl"), "--trace-steps", "true",
+         cwd=str(tmp_path))
+    t = json.load(open(tmp_path / "tl.rank0.json"))
+    spans = [e for e in t["traceEvents"] if e["ph"] == "X"]
+    names = [e["name"] for e in spans]
+    assert "warmup" in names and "timed_loop" in names and sum(n.startswith("step ") for n in names) == 12
+    assert all(e["dur"] >= 0 and e["ts"] >= 0 for e in spans)
