@@ -136,9 +136,12 @@ class TorchComm(Comm):
     peer fabric).
     """
 
-    def __init__(self, device_type: str = "cpu", init: bool = True, timeout_s: int = 600) -> None:
+    def __init__(self, device_type: str = "cpu", init: bool = True, timeout_s: Optional[int] = None) -> None:
         import datetime
         import torch.distributed as dist
+
+        if timeout_s is None:      # how long a collective / p2p call waits for a rank that never arrives
+            timeout_s = int(os.environ.get("IGG_B200_TIMEOUT_S", "600"))
 
         self._dist = dist
         self._owns_pg = False

@@ -12,6 +12,7 @@ export IGG_B200_TRANSPORT=${IGG_B200_TRANSPORT:-peer}
 # Per dimension (upstream: IGG_ROCMAWARE_MPI_DIMX/_DIMY/_DIMZ): with transport nccl or host,
 # IGG_B200_TRANSPORT_DIMX / _DIMY / _DIMZ = nccl | host overrides the staging of that dimension's messages.
 
+# IGG_B200_TIMEOUT_S (600): how long host-side collectives / p2p calls wait for a rank that never arrives.
 # Kernel tuning knobs (defaults are the measured best on B200; see profiles/):
 #   IGG_TMA_RPT    4  = rows per consumer thread (16 consumer warps + 1 producer warp per CTA)
 #   IGG_TILE_BAND  0  = row-major tile order (N > 0: bands of N tile columns)

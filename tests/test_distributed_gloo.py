@@ -61,3 +61,32 @@ def test_checkpoint_and_resume_through_the_perf_app(tmp_path):
 def test_ring_smoke_test_over_gloo():
     outs = run_workers("ring_gloo.py", 4)
     assert all("ok" in o for o in outs)
+
+
+def test_a_dead_rank_is_detected_not_waited_for():
+    """Fault injection: rank 1 of 2 exits abruptly; rank 0's next ``update_halo`` raises within the configured
+    time-out (``IGG_B200_TIMEOUT_S``) instead of hanging."""
+    import subprocess
+    import sys as _sys
+    from mp_util import ROOT, free_port
+    import os as _os
+    port = free_port()
+    procs = []
+    for r in range(2):
+        env = dict(_os.environ)
+        env.update({"RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": "2", "LOCAL_WORLD_SIZE": "2",
+                    "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "OMP_NUM_THREADS": "1",
+                    "IGG_B200_TIMEOUT_S": "20", "PYTHONPATH": ROOT + _os.pathsep + env.get("PYTHONPATH", "")})
+        procs.append(subprocess.Popen([_sys.executable, _os.path.join(ROOT, "tests", "workers", "fault_gloo.py")],
+                                      env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = []
+    for p in procs:
+        try:
+            out, _ = p.communicate(timeout=120)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise AssertionError("survivor hung on a dead neighbour")
+        outs.append(out)
+    assert procs[1].returncode == 7
+    assert procs[0].returncode == 0 and "failure detected" in outs[0], outs[0]
