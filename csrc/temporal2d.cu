@@ -153,21 +153,15 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         const int y = it.yb + 2 * cp;
         mbar_wait(&fullT[tq % SNT], (tq / SNT) & 1);
         for (int b = 0; b < it.nbi; ++b) {
-            const unsigned qb = tq + b, qc = cq + b, qm = mq + b;
+            const unsigned qb = tq + b, qc = cq + b;
             if (b + 1 < it.nbi) mbar_wait(&fullT[(qb + 1) % SNT], ((qb + 1) / SNT) & 1);
             mbar_wait(&fullC[qc % SNC], (qc / SNC) & 1);
-            const double* curT = ringT + (qb % SNT) * BLK;
-            const double* prevT = b > 0 ? ringT + ((qb + SNT - 1) % SNT) * BLK : curT;
-            const double* nextT = b + 1 < it.nbi ? ringT + ((qb + 1) % SNT) * BLK : curT;
-            const double* curC = ringC + (qc % SNC) * BLK;
-            const double* prevC = b > 0 ? ringC + ((qc + SNC - 1) % SNC) * BLK : curC;
-            double* curM = ringM + (qm % SNM) * BLK;
-            const double* prevM = ringM + ((qm + SNM - 1) % SNM) * BLK;
+            const BlockPtrs bp = block_ptrs(ringT, ringC, ringM, BLK, tq, cq, mq, b, it.nbi);
             const int xb = it.xin0 + b * SRB;
 
             double oA[RPT], oB[RPT];
             unsigned wA, wB;
-            step1_rows<SRB, RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, nx, ny, ph1, p.ml, inner, oA, oB);
+            step1_rows<SRB, RPT>(bp.prevT, bp.curT, bp.nextT, bp.curC, bp.curM, cp, rg, xb, it.yb, nx, ny, ph1, p.ml, inner, oA, oB);
             if (diag) {
                 step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, ny, wA, wB);
 #pragma unroll
@@ -180,12 +174,12 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
             if ((tid & 31) == 0 && b > 0) mbar_arrive_(&emptyT[(qb + SNT - 1) % SNT]);   // T block b-1 is done
             consumer_sync_(CONSUMERS);                                                   // mid block b complete
 
-            step2_rows<SRB, RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, ny, ph2, oA, oB, wA, wB);
+            step2_rows<SRB, RPT>(bp.prevM, bp.curM, bp.prevC, bp.curC, cp, rg, xb, it.yb, x_lo, x_hi, ny, ph2, oA, oB, wA, wB);
 #pragma unroll
             for (int r = 0; r < RPT; ++r) {
                 const bool a = (wA >> r) & 1u, c = (wB >> r) & 1u;
                 if (a | c) {
-                    const int x = xb - 1 + rg * RPT + r;
+                    const int x = step2_row(xb, rg, RPT, r);
                     double* out = p.T2 + (size_t)x * ny + y;
                     if (a && c) {
                         st_cs_f64x2(out, oA[r], oB[r]);

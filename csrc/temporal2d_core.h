@@ -175,6 +175,32 @@ T2_HD bool item_is_inner(const Geom& g, const Item& it) {
     return it.xin0 >= 1 && it.xin0 + it.nbi * g.srb - 1 <= g.nx - 2 && it.yb >= 1 && it.yb + BW - 1 <= g.ny - 2;
 }
 
+// ---- ring slots of block b of an item --------------------------------------------------------------------
+// tq / cq / mq count the blocks this CTA has streamed through the T / Cp / mid rings before the item.
+struct BlockPtrs {
+    const double *prevT, *curT, *nextT;   // T blocks b-1, b, b+1 (cur when they do not exist: never used then)
+    const double *prevC, *curC;           // Cp blocks b-1, b
+    const double* prevM;                  // mid block b-1 (garbage for b == 0: masked)
+    double* curM;                         // mid block b, written by step 1
+};
+
+T2_HD BlockPtrs block_ptrs(double* ringT, double* ringC, double* ringM, int blk, unsigned tq, unsigned cq,
+                           unsigned mq, int b, int nbi) {
+    const unsigned qb = tq + b, qc = cq + b, qm = mq + b;
+    BlockPtrs p;
+    p.curT = ringT + (qb % SNT) * blk;
+    p.prevT = b > 0 ? ringT + ((qb + SNT - 1) % SNT) * blk : p.curT;
+    p.nextT = b + 1 < nbi ? ringT + ((qb + 1) % SNT) * blk : p.curT;
+    p.curC = ringC + (qc % SNC) * blk;
+    p.prevC = b > 0 ? ringC + ((qc + SNC - 1) % SNC) * blk : p.curC;
+    p.curM = ringM + (qm % SNM) * blk;
+    p.prevM = ringM + ((qm + SNM - 1) % SNM) * blk;
+    return p;
+}
+
+// global row of output r of thread row-group rg in step 2 of the block whose first row is xb (one row behind)
+T2_HD int step2_row(int xb, int rg, int rpt, int r) { return xb - 1 + rg * rpt + r; }
+
 // ---- step 1: mid values of block b --------------------------------------------------------------------
 // Thread (cp, rg) owns box columns 2cp, 2cp+1 and the block rows rg*RPT ... rg*RPT+RPT-1.
 // prevT / nextT: blocks b-1 / b+1 (any readable block when they do not exist: the rows that would need them

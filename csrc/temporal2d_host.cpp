@@ -56,23 +56,17 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
             const bool inner = item_is_inner(g, it);
             load_box(T, g.nx, g.ny, it.xin0, it.yb, SRB, ringT + (tq % SNT) * BLK);
             for (int b = 0; b < it.nbi; ++b) {
-                const unsigned qb = tq + b, qc = cq + b, qm = mq + b;
+                const unsigned qb = tq + b, qc = cq + b;
                 if (b + 1 < it.nbi)
                     load_box(T, g.nx, g.ny, it.xin0 + (b + 1) * SRB, it.yb, SRB, ringT + ((qb + 1) % SNT) * BLK);
                 load_box(Cp, g.nx, g.ny, it.xin0 + b * SRB, it.yb, SRB, ringC + (qc % SNC) * BLK);
-                const double* curT = ringT + (qb % SNT) * BLK;
-                const double* prevT = b > 0 ? ringT + ((qb + SNT - 1) % SNT) * BLK : curT;
-                const double* nextT = b + 1 < it.nbi ? ringT + ((qb + 1) % SNT) * BLK : curT;
-                const double* curC = ringC + (qc % SNC) * BLK;
-                const double* prevC = b > 0 ? ringC + ((qc + SNC - 1) % SNC) * BLK : curC;
-                double* curM = ringM + (qm % SNM) * BLK;
-                const double* prevM = ringM + ((qm + SNM - 1) % SNM) * BLK;
+                const BlockPtrs bp = block_ptrs(ringT, ringC, ringM, BLK, tq, cq, mq, b, it.nbi);
                 const int xb = it.xin0 + b * SRB;
                 for (int rg = 0; rg < NRG; ++rg)
                     for (int cp = 0; cp < NPAIR; ++cp) {
                         double mA[RPT], mB[RPT];
                         unsigned wA, wB;
-                        step1_rows<SRB, RPT>(prevT, curT, nextT, curC, curM, cp, rg, xb, it.yb, g.nx, g.ny, ph1, ml, inner, mA, mB);
+                        step1_rows<SRB, RPT>(bp.prevT, bp.curT, bp.nextT, bp.curC, bp.curM, cp, rg, xb, it.yb, g.nx, g.ny, ph1, ml, inner, mA, mB);
                         step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, g.ny, wA, wB);
                         for (int r = 0; r < RPT; ++r) {
                             if ((wA >> r) & 1u) { d1max = mA[r] > d1max ? mA[r] : d1max; d1sum += mA[r]; }
@@ -84,11 +78,11 @@ void emulate(const double* T, double* T2, const double* Cp, const Geom& g, const
                     for (int cp = 0; cp < NPAIR; ++cp) {
                         double oA[RPT], oB[RPT];
                         unsigned wA, wB;
-                        step2_rows<SRB, RPT>(prevM, curM, prevC, curC, cp, rg, xb, it.yb, x_lo, x_hi, g.ny, ph2, oA, oB,
+                        step2_rows<SRB, RPT>(bp.prevM, bp.curM, bp.prevC, bp.curC, cp, rg, xb, it.yb, x_lo, x_hi, g.ny, ph2, oA, oB,
                                         wA, wB);
                         const int y = it.yb + 2 * cp;
                         for (int r = 0; r < RPT; ++r) {
-                            const int x = xb - 1 + rg * RPT + r;
+                            const int x = step2_row(xb, rg, RPT, r);
                             if ((wA >> r) & 1u) {
                                 T2[(size_t)x * g.ny + y] = oA[r];
                                 d2max = oA[r] > d2max ? oA[r] : d2max;
