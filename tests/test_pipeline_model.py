@@ -175,6 +175,15 @@ class Model:
                 del waiting[n]
 
 
+def _ring_depths():
+    """The depths the kernel is actually built with (csrc/temporal2d_core.h)."""
+    import os
+    import re
+    src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "csrc",
+                            "temporal2d_core.h")).read()
+    return tuple(int(re.search(rf"constexpr int {n} = (\d+);", src).group(1)) for n in ("SNT", "SNC", "SNM"))
+
+
 def _items(rng, n):
     return [rng.choice([1, 1, 2, 3, 5, 8, 16]) for _ in range(n)]
 
@@ -182,8 +191,10 @@ def _items(rng, n):
 @pytest.mark.parametrize("ncw", [2, 4, 16])
 def test_pipeline_of_the_two_step_kernel(ncw):
     rng = random.Random(ncw)
+    snt, snc, snm = _ring_depths()
+    assert (snt, snc, snm) == (4, 3, 3)
     for seed in range(30):
-        Model(_items(rng, 12), ncw, snt=4, snc=3, snm=3, seed=seed).run()
+        Model(_items(rng, 12), ncw, snt=snt, snc=snc, snm=snm, seed=seed).run()
 
 
 @pytest.mark.parametrize("depths", [(3, 3, 3), (4, 2, 3)])
