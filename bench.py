@@ -7,9 +7,20 @@ reported as the whole-job aggregate (sum over GPUs).  One rank per GPU; for N > 
 
 Two timed regions, both bracketed by barrier + ``torch.cuda.synchronize()``, max over ranks:
 
-* ``value``  -- K steps of the flagship fused kernel (stencil + in-kernel halo push), CUDA events;
+* ``value``  -- K steps of the flagship kernel (stencil + in-kernel halo push), CUDA events;
 * ``e2e``    -- K steps through the public ``Diffusion2D.step_controlled`` API: per step the parameters
-  travel host(pinned) -> device, the step runs, ``[max, sum]`` of the new field travel device -> host.
+  travel host(pinned) -> device, the step runs, ``[max, sum]`` of the new field travel device -> host
+  (pipelined: step k+1 is queued before the host waits for step k's diagnostic).
+
+Outside both timed regions, on the same ranks (``--no-verify`` / ``--no-baseline`` skip them):
+
+* ``verify``       -- the benchmarked mode against the serial baseline structure (direct-load kernel, swap,
+  ``update_halo`` over NCCL) from the same initial condition at the benchmark size, every cell incl. halos;
+  and a small 254 x 254 global problem (the reference's published field, ``docs/Temp_4_252_252.png``) run for
+  200 steps on the same rank layout against the single-domain CPU oracle.  A mismatch makes the run fail.
+* ``vs_baseline``  -- the same-box baseline BASELINE.json defines (separate stencil kernel + pack / NCCL
+  send-recv / unpack), timed in this process with the same K/W: ``value / value_of(nccl arm)``.  It is NOT a
+  ratio against the Julia reference (that arm is unavailable here).
 
 ``--impl reference``: the reference is Julia + AMDGPU.jl + ROCm-aware MPI; it cannot be installed or run
 here, so that arm reports ``unavailable``.  ``--impl nccl`` runs the same-box baseline
@@ -41,6 +52,10 @@ def parse_args():
     p.add_argument("--ny", type=int, default=16384)
     p.add_argument("--b-width", type=int, nargs=2, default=[16, 4])
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-verify", action="store_true")
+    p.add_argument("--no-baseline", action="store_true")
+    p.add_argument("--kernel", default=os.environ.get("IGG_BENCH_KERNEL", "auto"), choices=["auto", "fused", "temporal"],
+                   help="what --impl ours runs: one step per pass (fused) or two steps per pass (temporal)")
     return p.parse_args()
 
 
@@ -95,6 +110,138 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+IMPLS = {"ours": ("fused", "tma", "peer"), "hide": ("hide", "tma", "peer"), "direct": ("fused", "direct", "peer"),
+         "temporal": ("temporal", "tma", "peer"), "plain_peer": ("plain", "tma", "peer"),
+         "nccl_tma": ("plain", "tma", "nccl"), "nccl": ("plain", "direct", "nccl")}
+DEFAULT_OURS = "temporal"        # what `--kernel auto` resolves to (the faster of the two on B200, see profiles/)
+
+
+def time_steps(s, g, W, K, native, torch):
+    """W untimed + K timed steps of solver ``s``: (ms per step, max over ranks; native launches in the region)."""
+    s.begin()
+    s.step(W)
+    g.comm.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0 = native.launch_count()
+    e0.record()
+    s.step(K)
+    e1.record()
+    torch.cuda.synchronize()
+    n1 = native.launch_count()
+    g.comm.barrier()
+    ms = g.comm.allreduce_max(e0.elapsed_time(e1)) / K
+    s.finish()
+    return ms, int(n1 - n0)
+
+
+def time_e2e(s, g, W, K, pair, torch):
+    """K end-to-end steps through the public control API (pipelined), device clock + host wall clock."""
+    s.begin()
+    for _ in range(W):
+        s.step_controlled_pair(pipelined=True) if pair else s.step_controlled(pipelined=True)
+    s.drain_controlled()
+    g.comm.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ee0.record()
+    seen = 0
+    last = None
+    if pair:
+        for _ in range(K // 2):
+            r = s.step_controlled_pair(pipelined=True)
+            if r is not None:
+                last, seen = r[1], seen + 2
+        for _ in range(K % 2):
+            r = s.step_controlled(pipelined=True)
+            if r is not None:
+                last, seen = (r[1] if isinstance(r[0], tuple) else r), seen + (2 if isinstance(r[0], tuple) else 1)
+    else:
+        for _ in range(K):
+            r = s.step_controlled(pipelined=True)
+            if r is not None:
+                last, seen = r, seen + 1
+    for r in s.drain_controlled():                      # the last diagnostics: still inside the timed region
+        if isinstance(r[0], tuple):
+            last, seen = r[1], seen + 2
+        else:
+            last, seen = r, seen + 1
+    ee1.record()
+    torch.cuda.synchronize()
+    dt_wall = time.perf_counter() - t0
+    g.comm.barrier()
+    ms = g.comm.allreduce_max(ee0.elapsed_time(ee1)) / K
+    ms_wall = g.comm.allreduce_max(dt_wall * 1e3) / K
+    s.finish()
+    assert seen == K, (seen, K)
+    return ms, ms_wall, last
+
+
+def verify(igg, Diffusion2D, torch, nx, ny, mode, dims, nprocs):
+    """Correctness of the benchmarked mode on THIS rank layout (outside the timed regions)."""
+    from rocm_mpi_b200.ops import reference as ref
+    out = {"flag_timeouts": 0}
+    g = igg.global_grid()
+    # (a) benchmark size: `mode` vs the reference's serial structure with the direct-load kernel and NCCL
+    nsteps = 7                                  # odd: the two-step mode ends with a one-step launch
+    a = Diffusion2D(nx, ny, mode=mode, variant="tma")
+    b = Diffusion2D(nx, ny, mode="plain", variant="direct", transport="nccl" if nprocs > 1 else "peer")
+    try:
+        for s in (a, b):
+            s.begin()
+            s.step(nsteps)
+            s.finish()
+        torch.cuda.synchronize()
+        err = float((a.T - b.T).abs().max())
+    except RuntimeError as e:
+        if "timed out" not in str(e):
+            raise
+        out["flag_timeouts"] += 1
+        err = float("inf")
+    out["max_abs_err_vs_nccl"] = g.comm.allreduce_max(err)
+    out["vs_nccl"] = f"{mode} vs plain+direct+nccl, local {nx}x{ny}, {nsteps} steps, all cells incl. halos"
+    a.close()
+    b.close()
+    igg.finalize_global_grid(finalize_dist=False)
+    # (b) the reference's published problem (254 x 254 global, docs/Temp_4_252_252.png) on this layout vs the
+    #     single-domain fp64 CPU oracle, 200 steps, gathered halo-free field
+    if 252 % dims[0] or 252 % dims[1]:
+        out["max_abs_err_vs_oracle"] = None
+        out["vs_oracle"] = f"skipped: 252 is not divisible by dims {dims}"
+    else:
+        lx_, ly_ = 252 // dims[0] + 2, 252 // dims[1] + 2
+        small_mode = mode if ly_ % 2 == 0 else "fused"
+        igg.init_global_grid(lx_, ly_, 1, dimx=dims[0], dimy=dims[1], quiet=True, init_dist=False)
+        g = igg.global_grid()
+        s = Diffusion2D(lx_, ly_, mode=small_mode, variant="tma" if ly_ % 2 == 0 else "direct")
+        err = 0.0
+        try:
+            s.begin()
+            s.step(200)
+            s.finish()
+            Tv = igg.gather_interior(s.T)
+            if g.me == 0:
+                want, _ = ref.oracle_2d(igg.nx_g(), igg.ny_g(), 200, form="perf")
+                err = float((Tv - want[1:-1, 1:-1]).abs().max())
+                out["max_T_v"] = float(Tv.max())
+        except RuntimeError as e:
+            if "timed out" not in str(e):
+                raise
+            out["flag_timeouts"] += 1
+            err = float("inf")
+        out["max_abs_err_vs_oracle"] = g.comm.allreduce_max(err)
+        out["vs_oracle"] = (f"{small_mode}, local {lx_}x{ly_} on {dims[0]}x{dims[1]} (global 254x254), 200 steps, "
+                            "gathered field vs single-domain CPU oracle")
+        s.close()
+        igg.finalize_global_grid(finalize_dist=False)
+    out["flag_timeouts"] = int(g.comm.allreduce_max(float(out["flag_timeouts"])))
+    out["tolerance"] = 1e-12
+    out["ok"] = bool(out["flag_timeouts"] == 0 and out["max_abs_err_vs_nccl"] <= 1e-12 and
+                     (out["max_abs_err_vs_oracle"] is None or out["max_abs_err_vs_oracle"] <= 1e-12))
+    return out
+
+
 def main() -> int:
     a = parse_args()
     if a.impl == "reference":
@@ -122,69 +269,54 @@ def main() -> int:
     nx, ny = a.nx, a.ny
     me, dims, nprocs, coords, _ = igg.init_global_grid(nx, ny, 1, quiet=True)
     g = igg.global_grid()
-    mode, variant, transport = {"ours": ("fused", "tma", "peer"), "hide": ("hide", "tma", "peer"),
-                                "direct": ("fused", "direct", "peer"),
-                                "temporal": ("temporal", "tma", "peer"),   # experimental: two steps per pass
-                                "plain_peer": ("plain", "tma", "peer"), "nccl_tma": ("plain", "tma", "nccl"),
-                                "nccl": ("plain", "direct", "nccl")}[a.impl]
+    mode, variant, transport = IMPLS[a.impl]
+    if a.impl == "ours":
+        kern = DEFAULT_OURS if a.kernel == "auto" else a.kernel
+        if kern == "temporal" and ny % 2 == 0:
+            mode = "temporal"
+    steps_per_pass = 2 if mode == "temporal" else 1
     s = Diffusion2D(nx, ny, mode=mode, variant=variant, transport=transport, b_width=a.b_width)
     A_eff = igg.a_eff((nx, ny))                      # GB per step per GPU
 
     # ---- device-timed region -------------------------------------------------------------------
-    s.begin()
-    s.step(W)
-    g.comm.barrier()
-    torch.cuda.synchronize()
     sampler = ClockSampler(g.device.index) if me == 0 else None
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n0 = native.launch_count()
-    e0.record()
-    s.step(K)
-    e1.record()
-    torch.cuda.synchronize()
-    n1 = native.launch_count()
-    g.comm.barrier()
-    ms = g.comm.allreduce_max(e0.elapsed_time(e1)) / K
-    s.finish()
+    ms, launches = time_steps(s, g, W, K, native, torch)
     t_eff = A_eff / (ms * 1e-3)
 
     # ---- end-to-end region ---------------------------------------------------------------------
     e2e = None
-    if not a.no_e2e:
-        s.begin()
-        pair = a.impl == "temporal"          # experimental: the host hands over / reads back two steps at a time
-        for _ in range(W):
-            s.step_controlled_pair() if pair else s.step_controlled()
-        g.comm.barrier()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ee0.record()
-        mx = 0.0
-        if pair:
-            for _ in range(K // 2):
-                _, (mx, sm) = s.step_controlled_pair()
-            for _ in range(K % 2):
-                mx, sm = s.step_controlled()
-        else:
-            for _ in range(K):
-                mx, sm = s.step_controlled()
-        ee1.record()
-        torch.cuda.synchronize()
-        dt_wall = time.perf_counter() - t0
-        g.comm.barrier()
-        # device clock (CUDA events around the whole loop: includes every gap the host causes), max over ranks;
-        # the host wall clock of the same region is reported next to it
-        ms_e2e = g.comm.allreduce_max(ee0.elapsed_time(ee1)) / K
-        ms_e2e_wall = g.comm.allreduce_max(dt_wall * 1e3) / K
-        s.finish()
+    if not a.no_e2e and mode in ("fused", "temporal") and variant == "tma":
+        pair = mode == "temporal"
+        ms_e2e, ms_e2e_wall, last = time_e2e(s, g, W, K, pair, torch)
         e2e = {"value": round(nprocs * A_eff / (ms_e2e * 1e-3), 2), "unit": "GB/s", "ms_per_step": round(ms_e2e, 5),
                "ms_per_step_host_wall": round(ms_e2e_wall, 5),
                "h2d_bytes_per_step": Diffusion2D.h2d_bytes_per_step,
-               "d2h_bytes_per_step": Diffusion2D.d2h_bytes_per_step, "last_max_T": mx,
-               "api": "rocm_mpi_b200.models.solver.Diffusion2D." + ("step_controlled_pair" if pair else "step_controlled")}
+               "d2h_bytes_per_step": Diffusion2D.d2h_bytes_per_step, "last_max_T": last[0] if last else None,
+               "pipeline": "step k+1 is queued before the host waits for step k's diagnostic; every step's copies "
+                           "are inside the timed region",
+               "api": "rocm_mpi_b200.models.solver.Diffusion2D." +
+                      ("step_controlled_pair(pipelined=True)" if pair else "step_controlled(pipelined=True)")}
     clocks = sampler.stop() if sampler is not None else None
+    s.close()
 
+    # ---- same-box baseline arms (BASELINE.json: separate stencil kernel + pack / NCCL p2p / unpack) ----------
+    base = {}
+    if not a.no_baseline and a.impl not in ("nccl", "nccl_tma"):
+        for name in ("nccl", "nccl_tma"):
+            bm, bv, bt = IMPLS[name]
+            sb = Diffusion2D(nx, ny, mode=bm, variant=bv, transport=bt if nprocs > 1 else "peer", b_width=a.b_width)
+            bms, _ = time_steps(sb, g, W, K, native, torch)
+            sb.close()
+            base[name] = {"ms_per_step": round(bms, 5), "value": round(nprocs * A_eff / (bms * 1e-3), 2)}
+
+    # ---- verification (own grids; leaves no grid behind) -----------------------------------------------------
+    ver = None
+    if not a.no_verify and mode in ("fused", "temporal", "hide"):
+        ver = verify(igg, Diffusion2D, torch, nx, ny, mode, dims, nprocs)
+    else:
+        igg.finalize_global_grid(finalize_dist=False)
+
+    rc = 0
     if me == 0:
         peaks = {}
         try:
@@ -193,25 +325,61 @@ def main() -> int:
         except Exception:
             pass
         hbm = peaks.get("hbm_gbs", 6650.0)
+        nvl = 770.0                                   # measured peer copy, GB/s per direction per GPU (profiling recipe)
+        # bytes this rank sends per step: one edge line per existing face neighbour (+ 8 B per corner); the
+        # two-step mode sends a mid line and an edge line per PAIR of steps -- the same per step
+        faces = [(0, -1), (0, 1), (1, -1), (1, 1)]
+        n_face = {0: 0, 1: 0}
+        for d, sgn in faces:
+            if dims[d] > 1:
+                n_face[d] += 1 if dims[d] == 2 else 2      # interior ranks have both neighbours (worst rank counts)
+        halo_bytes = 8 * (min(n_face[0], 2) * ny + min(n_face[1], 2) * nx)
+        hbm_term = A_eff / steps_per_pass / hbm * 1e3 if steps_per_pass > 1 else A_eff / hbm * 1e3
+        dram_bytes_step = A_eff / steps_per_pass if steps_per_pass > 1 else A_eff
+        nvl_term = halo_bytes / 1e9 / nvl * 1e3
+        roof_ms = max(hbm_term, nvl_term)
+        value = round(nprocs * t_eff, 2)
         out = {
             "metric": "T_eff effective memory throughput of diffusion_2D_perf (3*nx*ny*8 B / t_it), aggregate over GPUs",
-            "value": round(nprocs * t_eff, 2), "unit": "GB/s", "n_gpus": nprocs, "steps": K, "warmup": W,
-            "ms_per_step": round(ms, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "value": value, "unit": "GB/s", "n_gpus": nprocs, "steps": K, "warmup": W,
+            "ms_per_step": round(ms, 5), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": round(value / base["nccl"]["value"], 4) if base else None,
             "dtype": "fp64", "data": "synthetic (Gaussian initial condition, Cp = 1; no datasets exist for this app)",
             "impl": a.impl,
-            "config": {"model": "diffusion_2D_perf", "local_grid": [nx, ny], "global_grid": [igg.nx_g(), igg.ny_g()],
+            "config": {"model": "diffusion_2D_perf", "local_grid": [nx, ny], "global_grid": [dims[0] * (nx - 2) + 2,
+                                                                                              dims[1] * (ny - 2) + 2],
                        "global_batch": nprocs * nx * ny, "seq_len": None,
                        "parallelism": f"cartesian {dims[0]}x{dims[1]} domain decomposition, halo width 1",
                        "step": f"mode={mode} kernel={variant} transport={transport} b_width={list(a.b_width)}",
+                       "steps_per_pass": steps_per_pass,
                        "l2": "inputs exceed L2 (3 x %.2f GiB per GPU per step vs 126 MB)" % (nx * ny * 8 / 2**30)},
             "per_gpu_T_eff": round(t_eff, 2),
-            "roofline": {"hbm_gbs": hbm, "source": "MEASURED_PEAKS.json" if peaks else "fallback",
-                         "fraction_of_hbm_peak": round(t_eff / hbm, 4)},
-            "e2e": e2e, "gpu_launches": int(n1 - n0), "clocks": clocks,
+            "roofline": {"hbm_gbs": hbm, "nvlink_gbs_per_dir": nvl,
+                         "source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                         "fraction_of_hbm_peak": round(t_eff / hbm, 4),
+                         "dram_bytes_per_step_algorithmic": int(dram_bytes_step * 1e9),
+                         "hbm_term_ms": round(hbm_term, 5), "halo_bytes_per_step": halo_bytes,
+                         "nvlink_term_ms": round(nvl_term, 6), "bound": "hbm" if hbm_term >= nvl_term else "nvlink",
+                         "fraction_of_roofline": round(roof_ms / ms, 4),
+                         "note": ("T_eff keeps the reference's definition (3 arrays of the grid per STEP, "
+                                  "scripts/diffusion_2D_perf.jl:55-57); a two-step pass moves those bytes once per TWO "
+                                  "steps, so T_eff can exceed the copy bandwidth while the DRAM traffic does not")
+                         if steps_per_pass > 1 else None},
+            "vs_baseline_arms": ({"kind": "same-box baseline defined by BASELINE.json (separate stencil kernel + pack / "
+                                          "NCCL p2p / unpack), timed in this process; NOT the Julia reference",
+                                  **{k: {"ratio": round(value / v["value"], 4), **v} for k, v in base.items()}}
+                                 if base else None),
+            "verify": ver,
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(out), flush=True)
-    igg.finalize_global_grid()
-    return 0
+        if ver is not None and not ver["ok"]:
+            print("bench.py: VERIFICATION FAILED", ver, file=sys.stderr)
+            rc = 3
+    if ver is not None and not ver["ok"]:
+        rc = 3
+    g.comm.finalize()
+    return rc
 
 
 if __name__ == "__main__":

@@ -190,6 +190,10 @@ __device__ __forceinline__ bool wait_flag_ge_relaxed(const uint64_t* p, uint64_t
     return true;
 }
 
+// max that propagates NaN (fmax drops it): a blown-up field must show up in the max diagnostic the way it does in
+// the reference's maximum(T_v) (scripts/diffusion_2D_perf_hide.jl:115)
+__device__ __forceinline__ double max_nan(double a, double b) { return (a > b || a != a) ? a : b; }
+
 // streaming (evict-first) 16-byte / 8-byte global stores and read-only loads
 __device__ __forceinline__ void st_cs_f64x2(double* p, double a, double b) {
     asm volatile("st.global.cs.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");

@@ -29,35 +29,179 @@ static GetAddressRangeFn address_range_fn() {
 }
 
 // ---- one-launch update_halo ---------------------------------------------------------------------
+// All boxes of all fields are flattened into one list of "units" that the CTAs share evenly:
+//   * a box whose rows are long contiguous runs with equal 16-byte phase on both sides (y-planes of a 2-D field,
+//     faces of a 3-D field that keep the last dimension) moves 16-byte vectors: unit 0 of a row is the scalar
+//     head + tail, units 1.. are the vectors;
+//   * every other box (x-planes of a row-major field: one element per row, strided) moves single elements.
+// A thread keeps four units in flight (independent loads, then the four stores).  The strided local loads do
+// not need the neighbours' permission, so the first batch is fetched BEFORE the ready handshake is awaited:
+// the handshake's NVLink round trip overlaps the load latency instead of preceding it.
 constexpr int HX_THREADS = 256;
+constexpr int HX_MAX_BOXES = 27 * IGG_MAX_HALO_FIELDS;
+constexpr int HX_BATCH = 4;
+
+struct HxBox {
+    const unsigned char* src;       // address of the box's first element in my array
+    unsigned char* dst;             // address of its destination in the neighbour's array
+    unsigned long long pitch_a, pitch_b;   // bytes between consecutive a / b indices (same on both sides)
+    unsigned int e1;                // extent[1]
+    unsigned int upr;               // units per row
+    unsigned int run;               // elements per row
+    unsigned int eb;                // element bytes
+    unsigned int head;              // scalar elements before the first 16-byte vector (vector boxes)
+    unsigned int nvec;              // 16-byte vectors per row (0 = scalar box)
+};
+
+__device__ __forceinline__ void hx_setup_box(const igg_halo_xfer& t, HxBox& b, unsigned long long& units) {
+    const unsigned long long eb = (unsigned long long)t.elem_bytes;
+    b.eb = (unsigned int)eb;
+    b.pitch_b = (unsigned long long)t.n[2] * eb;
+    b.pitch_a = (unsigned long long)t.n[1] * b.pitch_b;
+    const unsigned long long so = ((unsigned long long)t.src_start[0] * t.n[1] + t.src_start[1]) * t.n[2] + t.src_start[2];
+    const unsigned long long dof = ((unsigned long long)t.dst_start[0] * t.n[1] + t.dst_start[1]) * t.n[2] + t.dst_start[2];
+    b.src = (const unsigned char*)t.src + so * eb;
+    b.dst = (unsigned char*)t.dst + dof * eb;
+    b.e1 = (unsigned int)t.extent[1];
+    b.run = (unsigned int)t.extent[2];
+    const unsigned long long rows = (unsigned long long)t.extent[0] * t.extent[1];
+    const unsigned long long run_bytes = (unsigned long long)b.run * eb;
+    const unsigned int ps = (unsigned int)((uintptr_t)b.src & 15), pd = (unsigned int)((uintptr_t)b.dst & 15);
+    const bool vec = run_bytes >= 64 && ps == pd && (b.pitch_b & 15) == 0 && (ps % eb) == 0;
+    if (vec) {
+        const unsigned int head_bytes = (16 - ps) & 15;
+        b.head = head_bytes / (unsigned int)eb;
+        b.nvec = (unsigned int)((run_bytes - head_bytes) / 16);
+        b.upr = 1 + b.nvec;
+    } else {
+        b.head = 0;
+        b.nvec = 0;
+        b.upr = b.run;
+    }
+    units = rows * b.upr;
+}
+
+__device__ __forceinline__ void hx_copy_elem(unsigned char* d, const unsigned char* s, unsigned int eb) {
+    switch (eb) {
+        case 8: *(uint64_t*)d = *(const uint64_t*)s; break;
+        case 4: *(uint32_t*)d = *(const uint32_t*)s; break;
+        case 2: *(uint16_t*)d = *(const uint16_t*)s; break;
+        default: *d = *s; break;
+    }
+}
 
 __global__ void __launch_bounds__(HX_THREADS) halo_exchange_kernel(const igg_halo_xfer* __restrict__ xf, int nx,
                                                                    const __grid_constant__ igg_halo_sync sy) {
+    __shared__ HxBox box[HX_MAX_BOXES];
+    __shared__ unsigned long long first_unit[HX_MAX_BOXES + 1];
+    __shared__ int abort_flag;
     const int tid = threadIdx.x;
     uint64_t* err = sy.my_bank + IGG_SLOT_ERR;
-    // (1) tell every neighbour that my halo cells may be overwritten (all earlier work on this
-    //     stream has finished), then wait for the same promise from them.  The promise I make to the
-    //     neighbour at offset o shows up in ITS bank under the opposite offset 26-o.
+    // (1) tell every neighbour that my halo cells may be overwritten (all earlier work on this stream has
+    //     finished).  The promise I make to the neighbour at offset o shows up in ITS bank under 26-o.
     if (blockIdx.x == 0 && tid < 27 && sy.peer_bank[tid])
         st_release_sys(sy.peer_bank[tid] + IGG_SLOT_READY + (26 - tid), sy.epoch);
-    if (tid < 27 && sy.peer_bank[tid]) wait_flag_ge(sy.my_bank + IGG_SLOT_READY + tid, sy.epoch, err);
+    if (tid == 0) abort_flag = 0;
+    for (int k = tid; k < nx; k += HX_THREADS) {
+        unsigned long long u;
+        hx_setup_box(xf[k], box[k], u);
+        first_unit[k + 1] = u;
+    }
     __syncthreads();
-    // (2) store every box into the neighbours' arrays
-    for (int k = 0; k < nx; ++k) {
-        const igg_halo_xfer t = xf[k];
-        const size_t e2 = (size_t)t.extent[2], e1 = (size_t)t.extent[1];
-        const size_t count = (size_t)t.extent[0] * e1 * e2;
-        for (size_t e = (size_t)blockIdx.x * HX_THREADS + tid; e < count; e += (size_t)gridDim.x * HX_THREADS) {
-            const size_t c = e % e2, b = (e / e2) % e1, a = e / (e1 * e2);
-            const size_t si = ((a + t.src_start[0]) * t.n[1] + (b + t.src_start[1])) * t.n[2] + (c + t.src_start[2]);
-            const size_t di = ((a + t.dst_start[0]) * t.n[1] + (b + t.dst_start[1])) * t.n[2] + (c + t.dst_start[2]);
-            switch (t.elem_bytes) {
-                case 8: ((uint64_t*)t.dst)[di] = ((const uint64_t*)t.src)[si]; break;
-                case 4: ((uint32_t*)t.dst)[di] = ((const uint32_t*)t.src)[si]; break;
-                case 2: ((uint16_t*)t.dst)[di] = ((const uint16_t*)t.src)[si]; break;
-                default: ((uint8_t*)t.dst)[di] = ((const uint8_t*)t.src)[si]; break;
+    if (tid == 0) {
+        first_unit[0] = 0;
+        for (int k = 0; k < nx; ++k) first_unit[k + 1] += first_unit[k];
+    }
+    __syncthreads();
+    const unsigned long long total = first_unit[nx];
+    const unsigned long long per_cta = (total + gridDim.x - 1) / gridDim.x;
+    const unsigned long long u_begin = (unsigned long long)blockIdx.x * per_cta;
+    const unsigned long long u_end = u_begin + per_cta < total ? u_begin + per_cta : total;
+
+    // unit -> addresses.  kind: 0 = nothing, 1 = one element, 2 = 16-byte vector, 3 = head + tail of a row
+    auto locate = [&](unsigned long long u, const unsigned char*& s, unsigned char*& d, unsigned int& eb,
+                      unsigned int& aux) -> int {
+        if (u >= u_end) return 0;
+        int lo = 0, hi = nx - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (first_unit[mid] <= u) lo = mid; else hi = mid - 1;
+        }
+        const HxBox& b = box[lo];
+        const unsigned int ul = (unsigned int)(u - first_unit[lo]);
+        const unsigned int row = ul / b.upr, cu = ul - row * b.upr;
+        const unsigned int a = row / b.e1, bb = row - a * b.e1;
+        const unsigned long long off = (unsigned long long)a * b.pitch_a + (unsigned long long)bb * b.pitch_b;
+        s = b.src + off;
+        d = b.dst + off;
+        eb = b.eb;
+        if (b.nvec == 0) {
+            s += (size_t)cu * eb;
+            d += (size_t)cu * eb;
+            return 1;
+        }
+        if (cu == 0) {
+            aux = (unsigned int)lo;
+            return 3;
+        }
+        const size_t vo = (size_t)b.head * eb + (size_t)(cu - 1) * 16;
+        s += vo;
+        d += vo;
+        return 2;
+    };
+
+    bool ready_checked = false;
+    for (unsigned long long cbase = u_begin; cbase < u_end; cbase += (unsigned long long)HX_BATCH * HX_THREADS) {
+        // the loop bound is CTA-uniform, so the barrier below is reached by every thread
+        const unsigned char* s[HX_BATCH];
+        unsigned char* d[HX_BATCH];
+        unsigned int eb[HX_BATCH], aux[HX_BATCH];
+        int kind[HX_BATCH];
+        uint4 v[HX_BATCH];
+#pragma unroll
+        for (int q = 0; q < HX_BATCH; ++q) {
+            kind[q] = locate(cbase + (unsigned long long)q * HX_THREADS + tid, s[q], d[q], eb[q], aux[q]);
+            if (kind[q] == 2) {
+                v[q] = *(const uint4*)s[q];
+            } else if (kind[q] == 1) {
+                switch (eb[q]) {
+                    case 8: { const uint64_t w = *(const uint64_t*)s[q]; v[q].x = (uint32_t)w; v[q].y = (uint32_t)(w >> 32); } break;
+                    case 4: v[q].x = *(const uint32_t*)s[q]; break;
+                    case 2: v[q].x = *(const uint16_t*)s[q]; break;
+                    default: v[q].x = *s[q]; break;
+                }
             }
         }
+        if (!ready_checked) {
+            // (2) the neighbours' promise, awaited with the first batch of loads already in flight
+            if (tid < 27 && sy.peer_bank[tid] && !wait_flag_ge(sy.my_bank + IGG_SLOT_READY + tid, sy.epoch, err))
+                abort_flag = 1;
+            __syncthreads();
+            ready_checked = true;
+        }
+        if (abort_flag) break;      // a neighbour never became ready: store nothing (the error word is set)
+#pragma unroll
+        for (int q = 0; q < HX_BATCH; ++q) {
+            if (kind[q] == 2) {
+                *(uint4*)d[q] = v[q];
+            } else if (kind[q] == 1) {
+                switch (eb[q]) {
+                    case 8: *(uint64_t*)d[q] = (uint64_t)v[q].x | ((uint64_t)v[q].y << 32); break;
+                    case 4: *(uint32_t*)d[q] = v[q].x; break;
+                    case 2: *(uint16_t*)d[q] = (uint16_t)v[q].x; break;
+                    default: *d[q] = (unsigned char)v[q].x; break;
+                }
+            } else if (kind[q] == 3) {
+                const HxBox& b = box[aux[q]];
+                for (unsigned int e = 0; e < b.head; ++e) hx_copy_elem(d[q] + (size_t)e * b.eb, s[q] + (size_t)e * b.eb, b.eb);
+                const unsigned int done = b.head + b.nvec * (16u / b.eb);
+                for (unsigned int e = done; e < b.run; ++e) hx_copy_elem(d[q] + (size_t)e * b.eb, s[q] + (size_t)e * b.eb, b.eb);
+            }
+        }
+    }
+    if (!ready_checked) {           // CTA without units (more CTAs than work): still part of the protocol
+        if (tid < 27 && sy.peer_bank[tid] && !wait_flag_ge(sy.my_bank + IGG_SLOT_READY + tid, sy.epoch, err))
+            abort_flag = 1;
     }
     // (3) last CTA to finish releases the epoch to every neighbour
     __syncthreads();
@@ -155,13 +299,19 @@ int igg_ipc_export(const void* ptr, void* handle64, uint64_t* offset) {
     cudaIpcMemHandle_t h;
     IGG_CUDA_OK(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)));
     memcpy(handle64, &h, 64);
+    // The handle names the whole allocation; the tensor may start anywhere inside it (torch's caching
+    // allocator sub-allocates).  Without the allocation base the peers would be pointed at the wrong bytes,
+    // so failing to obtain it is an error, never "offset 0".
     *offset = 0;
     GetAddressRangeFn fn = address_range_fn();
-    if (fn) {
-        CUdeviceptr base = 0;
-        size_t size = 0;
-        if (fn(&base, &size, (CUdeviceptr)(uintptr_t)ptr) == CUDA_SUCCESS) *offset = (uint64_t)((uintptr_t)ptr - (uintptr_t)base);
+    CUdeviceptr base = 0;
+    size_t size = 0;
+    if (!fn || fn(&base, &size, (CUdeviceptr)(uintptr_t)ptr) != CUDA_SUCCESS) {
+        igg::set_error("igg_ipc_export: cannot resolve the allocation base of %p (cuMemGetAddressRange %s)", ptr,
+                       fn ? "failed" : "is unavailable");
+        return IGG_ERR_UNSUPPORTED;
     }
+    *offset = (uint64_t)((uintptr_t)ptr - (uintptr_t)base);
     return 0;
 }
 
@@ -184,15 +334,26 @@ int igg_can_access_peer(int dev, int peer_dev, int* can) {
     return 0;
 }
 
-int igg_halo_exchange_peer(const igg_halo_xfer* xfers_dev, int nxfers, const igg_halo_sync* sync, void* stream) {
+int igg_halo_exchange_peer_ex(const igg_halo_xfer* xfers_dev, int nxfers, const igg_halo_sync* sync, int ctas,
+                              void* stream) {
     IGG_REQUIRE(sync && sync->my_bank && sync->my_count_bank && nxfers >= 0 && (nxfers == 0 || xfers_dev),
                 "igg_halo_exchange_peer: bad arguments");
     IGG_REQUIRE(sync->epoch >= 1, "igg_halo_exchange_peer: epoch must be >= 1");
-    int grid = igg::sm_count() / 4;   // a quarter of the SMs saturates NVLink for plane-sized messages
+    IGG_REQUIRE(nxfers <= HX_MAX_BOXES, "igg_halo_exchange_peer: at most %d boxes per call (got %d)", HX_MAX_BOXES,
+                nxfers);
+    // `ctas` = what the caller derived from the bytes it moves (one CTA per 16 KB is plenty); 0 = a quarter
+    // of the SMs, which saturates NVLink for plane-sized messages
+    int grid = ctas > 0 ? ctas : igg::sm_count() / 4;
+    const int cap = igg::sm_count() * 2;         // all CTAs wait on flags: they must be co-resident
+    if (grid > cap) grid = cap;
     if (grid < 1) grid = 1;
     halo_exchange_kernel<<<grid, HX_THREADS, 0, (cudaStream_t)stream>>>(xfers_dev, nxfers, *sync);
     IGG_LAUNCH_CHECK();
     return 0;
+}
+
+int igg_halo_exchange_peer(const igg_halo_xfer* xfers_dev, int nxfers, const igg_halo_sync* sync, void* stream) {
+    return igg_halo_exchange_peer_ex(xfers_dev, nxfers, sync, 0, stream);
 }
 
 int igg_neighbor_barrier(const igg_halo_sync* sync, void* stream) {

@@ -79,7 +79,7 @@ struct RedScratch {
 __device__ __forceinline__ void block_reduce(double& mx, double& sm, double* sh_max, double* sh_sum) {
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
-        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+        mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
         sm += __shfl_xor_sync(0xffffffffu, sm, off);
     }
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
@@ -90,7 +90,7 @@ __device__ __forceinline__ void block_reduce(double& mx, double& sm, double* sh_
         sm = l < RED_THREADS / 32 ? sh_sum[l] : 0.0;
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) {
-            mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+            mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
             sm += __shfl_xor_sync(0xffffffffu, sm, off);
         }
     }
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(RED_THREADS) reduce_max_sum_kernel(const doubl
     double mx = -INFINITY, sm = 0.0;
     for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
         const double v = x[e];
-        mx = fmax(mx, v);
+        mx = igg::max_nan(mx, v);
         sm += v;
     }
     block_reduce(mx, sm, sh_max, sh_sum);
@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(RED_THREADS) reduce_max_sum_kernel(const doubl
         mx = -INFINITY;
         sm = 0.0;
         for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x) {
-            mx = fmax(mx, sc->pmax[b]);
+            mx = igg::max_nan(mx, sc->pmax[b]);
             sm += sc->psum[b];
         }
         block_reduce(mx, sm, sh_max, sh_sum);

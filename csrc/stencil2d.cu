@@ -238,8 +238,8 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
                 if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
             }
             if (diag) {
-                if (wA) { dmax = fmax(dmax, vA); dsum += vA; }
-                if (wB) { dmax = fmax(dmax, vB); dsum += vB; }
+                if (wA) { dmax = igg::max_nan(dmax, vA); dsum += vA; }
+                if (wB) { dmax = igg::max_nan(dmax, vB); dsum += vB; }
             }
             a = b;
             b = c;
@@ -260,7 +260,7 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
         auto block_fold = [&](double& mx, double& sm) {
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) {
-                mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
                 sm += __shfl_xor_sync(0xffffffffu, sm, off);
             }
             if ((tid & 31) == 0) { red[tid >> 5] = mx; red[32 + (tid >> 5)] = sm; }
@@ -270,7 +270,7 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
                 sm = tid < NCW ? red[32 + tid] : 0.0;
 #pragma unroll
                 for (int off = 16; off > 0; off >>= 1) {
-                    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                    mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
                     sm += __shfl_xor_sync(0xffffffffu, sm, off);
                 }
             }
@@ -289,7 +289,7 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
             dmax = -INFINITY;
             dsum = 0.0;
             for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS) {
-                dmax = fmax(dmax, p.diag->pmax[b2]);
+                dmax = igg::max_nan(dmax, p.diag->pmax[b2]);
                 dsum += p.diag->psum[b2];
             }
             block_fold(dmax, dsum);
@@ -464,8 +464,8 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
                     if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
                 }
                 if (diag) {
-                    if (wA) { dmax = fmax(dmax, vA); dsum += vA; }
-                    if (wB) { dmax = fmax(dmax, vB); dsum += vB; }
+                    if (wA) { dmax = igg::max_nan(dmax, vA); dsum += vA; }
+                    if (wB) { dmax = igg::max_nan(dmax, vB); dsum += vB; }
                 }
                 a = bb;
                 bb = c;
@@ -496,7 +496,7 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
         auto block_fold = [&](double& mx, double& sm) {
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) {
-                mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
                 sm += __shfl_xor_sync(0xffffffffu, sm, off);
             }
             if ((tid & 31) == 0) { red[tid >> 5] = mx; red[32 + (tid >> 5)] = sm; }
@@ -506,7 +506,7 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
                 sm = tid < NCW ? red[32 + tid] : 0.0;
 #pragma unroll
                 for (int off = 16; off > 0; off >>= 1) {
-                    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                    mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
                     sm += __shfl_xor_sync(0xffffffffu, sm, off);
                 }
             }
@@ -525,7 +525,7 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
             dmax = -INFINITY;
             dsum = 0.0;
             for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS) {
-                dmax = fmax(dmax, p.diag->pmax[b2]);
+                dmax = igg::max_nan(dmax, p.diag->pmax[b2]);
                 dsum += p.diag->psum[b2];
             }
             block_fold(dmax, dsum);
@@ -972,14 +972,50 @@ extern "C" int igg_diffusion2d_run(double* T, double* T2, const double* Cp, int 
 
 // One end-to-end controlled step, entirely from native code: parameters travel host(pinned) -> device, the
 // fused step runs (reading them from device memory and producing the in-kernel {max, sum} diagnostic), the
-// diagnostic travels device -> host(pinned), and the call returns when it has arrived.  This is what a host
-// control loop (adaptive time stepping, monitoring) executes per step.
-extern "C" int igg_diffusion2d_step_controlled(const double* T, double* T2, const double* Cp, int nx, int ny,
-                                               const double* params_host_pinned, double* params_dev,
-                                               double* diag_dev, void* diag_scratch, double* diag_host_pinned,
-                                               int bwx, int bwy, const igg_push2d* push, void* stream) {
-    IGG_REQUIRE(params_host_pinned && params_dev && diag_dev && diag_scratch && diag_host_pinned,
-                "igg_diffusion2d_step_controlled: null pointer");
+// diagnostic travels device -> host(pinned).  This is what a host control loop (adaptive time stepping,
+// monitoring) executes per step.  Two forms:
+//   igg_diffusion2d_step_controlled_submit   queues the three operations and records `done_event`; the caller
+//                                            waits for it (igg_event_wait) whenever it needs the diagnostic.  A
+//                                            loop that submits step k+1 BEFORE it waits for step k keeps the GPU
+//                                            busy (the reference's loop never blocks the device either:
+//                                            scripts/diffusion_2D_perf.jl:47-52); it needs two pinned slots.
+//   igg_diffusion2d_step_controlled          submit + wait (the host sees step k before step k+1 is queued).
+extern "C" int igg_event_create(void** event_out) {
+    IGG_REQUIRE(event_out, "igg_event_create: null pointer");
+    cudaEvent_t ev = nullptr;
+    IGG_CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    *event_out = (void*)ev;
+    return 0;
+}
+
+extern "C" int igg_event_destroy(void* event) {
+    if (event) IGG_CUDA_OK(cudaEventDestroy((cudaEvent_t)event));
+    return 0;
+}
+
+// Polling keeps the host thread on the CPU (no blocking-sync wake-up latency), which matters when the wait is
+// made once per ~1 ms step; spin = 0 blocks in cudaEventSynchronize instead.
+extern "C" int igg_event_wait(void* event, int spin) {
+    IGG_REQUIRE(event, "igg_event_wait: null event");
+    cudaEvent_t ev = (cudaEvent_t)event;
+    if (spin) {
+        cudaError_t q;
+        while ((q = cudaEventQuery(ev)) == cudaErrorNotReady) {
+        }
+        IGG_CUDA_OK(q);
+    } else {
+        IGG_CUDA_OK(cudaEventSynchronize(ev));
+    }
+    return 0;
+}
+
+extern "C" int igg_diffusion2d_step_controlled_submit(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                                      const double* params_host_pinned, double* params_dev,
+                                                      double* diag_dev, void* diag_scratch, double* diag_host_pinned,
+                                                      int bwx, int bwy, const igg_push2d* push, void* done_event,
+                                                      void* stream) {
+    IGG_REQUIRE(params_host_pinned && params_dev && diag_dev && diag_scratch && diag_host_pinned && done_event,
+                "igg_diffusion2d_step_controlled_submit: null pointer");
     cudaStream_t st = (cudaStream_t)stream;
     IGG_CUDA_OK(cudaMemcpyAsync(params_dev, params_host_pinned, 4 * sizeof(double), cudaMemcpyHostToDevice, st));
     igg_step_opts o;
@@ -989,20 +1025,21 @@ extern "C" int igg_diffusion2d_step_controlled(const double* T, double* T2, cons
     const int rc = igg_diffusion2d_step(T, T2, Cp, nx, ny, 0.0, 0.0, 0.0, 0.0, &o, 0, bwx, bwy, 1, push, stream);
     if (rc) return rc;
     IGG_CUDA_OK(cudaMemcpyAsync(diag_host_pinned, diag_dev, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
-    // Wait for the diagnostic.  Polling an event keeps the host thread on the CPU (no blocking-sync wake-up
-    // latency), which matters when this call is made once per ~1 ms step.
+    IGG_CUDA_OK(cudaEventRecord((cudaEvent_t)done_event, st));
+    return 0;
+}
+
+extern "C" int igg_diffusion2d_step_controlled(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                               const double* params_host_pinned, double* params_dev,
+                                               double* diag_dev, void* diag_scratch, double* diag_host_pinned,
+                                               int bwx, int bwy, const igg_push2d* push, void* stream) {
+    static thread_local cudaEvent_t ev = nullptr;
+    if (!ev) IGG_CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    const int rc = igg_diffusion2d_step_controlled_submit(T, T2, Cp, nx, ny, params_host_pinned, params_dev, diag_dev,
+                                                          diag_scratch, diag_host_pinned, bwx, bwy, push, (void*)ev,
+                                                          stream);
+    if (rc) return rc;
     static int spin = -1;
     if (spin < 0) spin = env_int("IGG_E2E_SPIN", 1);
-    if (spin) {
-        static thread_local cudaEvent_t ev = nullptr;
-        if (!ev) IGG_CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        IGG_CUDA_OK(cudaEventRecord(ev, st));
-        cudaError_t q;
-        while ((q = cudaEventQuery(ev)) == cudaErrorNotReady) {
-        }
-        IGG_CUDA_OK(q);
-    } else {
-        IGG_CUDA_OK(cudaStreamSynchronize(st));
-    }
-    return 0;
+    return igg_event_wait((void*)ev, spin);
 }

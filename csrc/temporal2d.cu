@@ -166,8 +166,8 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                 step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, ny, wA, wB);
 #pragma unroll
                 for (int r = 0; r < RPT; ++r) {
-                    if ((wA >> r) & 1u) { d1max = fmax(d1max, oA[r]); d1sum += oA[r]; }
-                    if ((wB >> r) & 1u) { d1max = fmax(d1max, oB[r]); d1sum += oB[r]; }
+                    if ((wA >> r) & 1u) { d1max = igg::max_nan(d1max, oA[r]); d1sum += oA[r]; }
+                    if ((wB >> r) & 1u) { d1max = igg::max_nan(d1max, oB[r]); d1sum += oB[r]; }
                 }
             }
             __syncwarp();
@@ -192,8 +192,8 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                         if (c) push_cell_2d(p.push, nx, ny, x, y + 1, oB[r]);
                     }
                     if (diag) {
-                        if (a) { d2max = fmax(d2max, oA[r]); d2sum += oA[r]; }
-                        if (c) { d2max = fmax(d2max, oB[r]); d2sum += oB[r]; }
+                        if (a) { d2max = igg::max_nan(d2max, oA[r]); d2sum += oA[r]; }
+                        if (c) { d2max = igg::max_nan(d2max, oB[r]); d2sum += oB[r]; }
                     }
                 }
             }
@@ -225,7 +225,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
 #pragma unroll
                 for (int off = 16; off > 0; off >>= 1) {
                     const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
-                    v[q] = (q & 1) ? v[q] + o : fmax(v[q], o);
+                    v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
                 }
             if ((tid & 31) == 0)
                 for (int q = 0; q < 4; ++q) red[q][tid >> 5] = v[q];
@@ -237,7 +237,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
 #pragma unroll
                     for (int off = 16; off > 0; off >>= 1) {
                         const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
-                        v[q] = (q & 1) ? v[q] + o : fmax(v[q], o);
+                        v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
                     }
                 }
             }
@@ -256,7 +256,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
             for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS)
                 for (int q = 0; q < 4; ++q) {
                     const double o = p.diag->part[q][b2];
-                    v[q] = (q & 1) ? v[q] + o : fmax(v[q], o);
+                    v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
                 }
             block_fold();
             if (tid == 0) {
@@ -368,7 +368,7 @@ extern "C" int igg_diffusion2d_step2(const double* T, double* T2, const double* 
     p.T2 = T2;
     static int srb = -1, rpt = -1;
     if (srb < 0) {
-        srb = env_int_("IGG_T2_SRB", 16) == 8 ? 8 : 16;
+        srb = env_int_("IGG_T2_SRB", 8) == 16 ? 16 : 8;      // 8: two CTAs per SM (0.675 vs 0.709 ms per step at 16384^2)
         rpt = env_int_("IGG_T2_RPT", 2) == 4 ? 4 : 2;
     }
     p.g = make_geom(nx, ny, srb, igg_temporal2d_default_rows(), push ? 1 : 0);
@@ -455,13 +455,16 @@ extern "C" int igg_diffusion2d_midlines(const double* T, const double* Cp, int n
 
 // One end-to-end PAIR of steps of a host control loop: H2D copy of both steps' {lam, dt, _dx, _dy} (64 B) from
 // pinned host memory, [mid lines to the neighbours,] the two-step pass with both in-kernel diagnostics, D2H copy
-// of {max1, sum1, max2, sum2} (32 B) into pinned host memory; returns when they have arrived.
-extern "C" int igg_diffusion2d_step2_controlled(const double* T, double* T2, const double* Cp, int nx, int ny,
-                                                const double* params_host_pinned, double* params_dev,
-                                                double* diag_dev, void* diag_scratch, double* diag_host_pinned,
-                                                const igg_push2d* push, const igg_mid2d* mid, void* stream) {
-    IGG_REQUIRE(params_host_pinned && params_dev && diag_dev && diag_scratch && diag_host_pinned,
-                "igg_diffusion2d_step2_controlled: null pointer");
+// of {max1, sum1, max2, sum2} (32 B) into pinned host memory.  `_submit` records `done_event` and returns (wait
+// with igg_event_wait; a loop that submits pass k+1 before waiting for pass k keeps the GPU busy); the plain form
+// returns when the diagnostics have arrived.
+extern "C" int igg_diffusion2d_step2_controlled_submit(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                                       const double* params_host_pinned, double* params_dev,
+                                                       double* diag_dev, void* diag_scratch,
+                                                       double* diag_host_pinned, const igg_push2d* push,
+                                                       const igg_mid2d* mid, void* done_event, void* stream) {
+    IGG_REQUIRE(params_host_pinned && params_dev && diag_dev && diag_scratch && diag_host_pinned && done_event,
+                "igg_diffusion2d_step2_controlled_submit: null pointer");
     cudaStream_t st = (cudaStream_t)stream;
     IGG_CUDA_OK(cudaMemcpyAsync(params_dev, params_host_pinned, 8 * sizeof(double), cudaMemcpyHostToDevice, st));
     int rc = 0;
@@ -476,12 +479,18 @@ extern "C" int igg_diffusion2d_step2_controlled(const double* T, double* T2, con
     rc = igg_diffusion2d_step2(T, T2, Cp, nx, ny, 0.0, 0.0, 0.0, 0.0, &o, push, mid, stream);
     if (rc) return rc;
     IGG_CUDA_OK(cudaMemcpyAsync(diag_host_pinned, diag_dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    IGG_CUDA_OK(cudaEventRecord((cudaEvent_t)done_event, st));
+    return 0;
+}
+
+extern "C" int igg_diffusion2d_step2_controlled(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                                const double* params_host_pinned, double* params_dev,
+                                                double* diag_dev, void* diag_scratch, double* diag_host_pinned,
+                                                const igg_push2d* push, const igg_mid2d* mid, void* stream) {
     static thread_local cudaEvent_t ev = nullptr;
     if (!ev) IGG_CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-    IGG_CUDA_OK(cudaEventRecord(ev, st));
-    cudaError_t q;
-    while ((q = cudaEventQuery(ev)) == cudaErrorNotReady) {
-    }
-    IGG_CUDA_OK(q);
-    return 0;
+    const int rc = igg_diffusion2d_step2_controlled_submit(T, T2, Cp, nx, ny, params_host_pinned, params_dev, diag_dev,
+                                                           diag_scratch, diag_host_pinned, push, mid, (void*)ev, stream);
+    if (rc) return rc;
+    return igg_event_wait((void*)ev, 1);
 }

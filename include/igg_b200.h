@@ -84,6 +84,22 @@ int igg_diffusion2d_step_controlled(const double* T, double* T2, const double* C
                                     void* diag_scratch, double* diag_host_pinned, int bwx, int bwy,
                                     const igg_push2d* push, void* stream);
 
+/* The same step without the wait: queues H2D, step and D2H on `stream` and records `done_event` (an event from
+ * igg_event_create).  A control loop that submits step k+1 before it waits for step k (igg_event_wait) never
+ * leaves the GPU idle -- the reference's loop does not block the device per step either
+ * (scripts/diffusion_2D_perf.jl:47-52).  The caller owns the slots: `params_host_pinned` must stay untouched
+ * until the event of its step has completed, so a depth-2 loop alternates two pinned parameter slots and two
+ * pinned diagnostic slots; `params_dev` / `diag_dev` are stream-ordered and can be shared. */
+int igg_diffusion2d_step_controlled_submit(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                           const double* params_host_pinned, double* params_dev, double* diag_dev,
+                                           void* diag_scratch, double* diag_host_pinned, int bwx, int bwy,
+                                           const igg_push2d* push, void* done_event, void* stream);
+/* Completion events for the submit forms (cudaEvent_t without timing).  igg_event_wait: spin != 0 polls
+ * (lowest latency, one host core busy), spin == 0 blocks. */
+int igg_event_create(void** event_out);
+int igg_event_destroy(void* event);
+int igg_event_wait(void* event, int spin);
+
 /* `nsteps` back-to-back launches of igg_diffusion2d_step (mode 0) from a native loop; step s reads T
  * (s even) or T2 (s odd).  `push_even` pushes into the neighbours' T2 and carries the epoch of step 0,
  * `push_odd` pushes into the neighbours' T; both NULL = no communication.
@@ -162,6 +178,11 @@ int igg_diffusion2d_step2_controlled(const double* T, double* T2, const double* 
                                      const double* params_host_pinned, double* params_dev, double* diag_dev,
                                      void* diag_scratch, double* diag_host_pinned, const igg_push2d* push,
                                      const igg_mid2d* mid, void* stream);
+/* Submit form of the pair (see igg_diffusion2d_step_controlled_submit): records `done_event`, does not wait. */
+int igg_diffusion2d_step2_controlled_submit(const double* T, double* T2, const double* Cp, int nx, int ny,
+                                            const double* params_host_pinned, double* params_dev, double* diag_dev,
+                                            void* diag_scratch, double* diag_host_pinned, const igg_push2d* push,
+                                            const igg_mid2d* mid, void* done_event, void* stream);
 int igg_diffusion2d_midlines(const double* T, const double* Cp, int nx, int ny, double lam, double dt, double _dx,
                              double _dy, const double* dev_params, const igg_push2d* push, const igg_mid2d* mid,
                              void* stream);
@@ -258,6 +279,11 @@ typedef struct igg_halo_sync {
     uint64_t epoch;
 } igg_halo_sync;
 int igg_halo_exchange_peer(const igg_halo_xfer* xfers_dev, int nxfers, const igg_halo_sync* sync, void* stream);
+/* same, with the number of CTAs chosen by the caller from the bytes it moves (0 = default); at most
+ * 27 * IGG_MAX_HALO_FIELDS boxes per call */
+#define IGG_MAX_HALO_FIELDS 8
+int igg_halo_exchange_peer_ex(const igg_halo_xfer* xfers_dev, int nxfers, const igg_halo_sync* sync, int ctas,
+                              void* stream);
 
 /* neighbour barrier on a bank: signal `epoch` into DATA slots of every neighbour, wait for theirs */
 int igg_neighbor_barrier(const igg_halo_sync* sync, void* stream);

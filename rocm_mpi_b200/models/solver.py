@@ -97,6 +97,7 @@ class Diffusion2D:
             self._rll = os.environ.get("IGG_RESIDENT_LL", "1") != "0"
             self._rland_len = max(nx, ny)
             self._rland = fabric_zeros((2 * 9 * self._rland_len * 2,), torch.int64) if self._rll else None
+        self._closed = False
         self._gbar = torch.zeros(1, dtype=torch.int64, device=dev)
         self._gbar_base = 0
         self._running = False
@@ -114,6 +115,11 @@ class Diffusion2D:
         self._params_pin = torch.zeros(4, dtype=torch.float64).pin_memory()
         self._diag_dev = torch.zeros(2, dtype=torch.float64, device=dev)
         self._diag_pin = torch.zeros(2, dtype=torch.float64).pin_memory()
+        # pipelined control loop (step_controlled(pipelined=True)): two slots of pinned parameters / diagnostics
+        # and a completion event each, so that step k+1 is queued before the host waits for step k
+        self._ctl_slots = None
+        self._ctl_pending = []       # [(slot index, is_pair)] oldest first
+        self._ctl_next = 0
         if mode == "temporal":       # a pass hands over two steps' parameters and returns two diagnostics
             self._params2_dev = torch.zeros(8, dtype=torch.float64, device=dev)
             self._params2_pin = torch.zeros(8, dtype=torch.float64).pin_memory()
@@ -144,6 +150,7 @@ class Diffusion2D:
 
     def finish(self) -> None:
         """Collective: all pushes have landed; after this the halos of ``T`` are valid."""
+        self.drain_controlled()
         if self._rflags is not None and self._running:
             torch.cuda.current_stream().synchronize()
             if int(self._rflags[9 * 16].item()) != 0:
@@ -155,6 +162,29 @@ class Diffusion2D:
         if self.plan is not None and self._running:
             self.plan.finish()
         self._running = False
+
+    def close(self) -> None:
+        """Collective: release what this solver took from the fabric (flag bank, mid lines, the peer-mapped
+        fields ``T`` / ``T2`` and the resident-mode buffers).  The solver is unusable afterwards; a sweep that
+        builds many solvers inside one grid calls this between them."""
+        if self._closed:
+            return
+        if self._running:
+            self.finish()
+        self._closed = True
+        if self.plan is not None:
+            fab = self.plan.fab
+            self.plan.close()
+            self.plan = None
+        if self.uses_peer:
+            from ..parallel.fabric import get_fabric
+            fab = get_fabric(self.g)
+            for name in ("T", "T2", "_rflags", "_rland"):
+                t = getattr(self, name, None)
+                if t is not None and t.data_ptr() in fab._owned:
+                    fab.free(t)
+                setattr(self, name, None)
+        self.T = self.T2 = self.Cp = None
 
     # -- stepping ---------------------------------------------------------------------------------
     def _kernel(self, mode: int, push, dev_params=None, diag_out=None) -> None:
@@ -285,11 +315,23 @@ class Diffusion2D:
                     update_halo(self.T, transport=self.transport)
             self.steps_done += 1
 
-    def step_controlled(self, lam: Optional[float] = None, dt: Optional[float] = None) -> Tuple[float, float]:
+    def step_controlled(self, lam: Optional[float] = None, dt: Optional[float] = None, *,
+                        pipelined: bool = False) -> Optional[Tuple[float, float]]:
         """One end-to-end step: parameters in through pinned memory, ``(max, sum)`` of the new field out.
 
         The diagnostic covers the cells this rank updated (its halo-free interior), i.e. the local part of
-        ``maximum(T_v)`` / ``sum(T_v)`` of the gathered field."""
+        ``maximum(T_v)`` / ``sum(T_v)`` of the gathered field.
+
+        ``pipelined=True`` (fused TMA kernel): the step is queued and the call returns the diagnostic of the
+        PREVIOUS pipelined step (``None`` the first time); ``drain_controlled()`` returns what is still in
+        flight.  Every step still moves 32 B in and 16 B out, but the device never idles waiting for the host --
+        the reference's loop does not block the device per step either (``scripts/diffusion_2D_perf.jl:47-52``)."""
+        if pipelined:
+            if not (self.mode == "fused" and self.variant == "tma"):
+                raise ValueError("pipelined control needs mode='fused', variant='tma' (or step_controlled_pair)")
+            return self._step_controlled_pipelined(lam, dt, pair=False)
+        if self._ctl_pending:
+            raise RuntimeError("pipelined steps are in flight: call drain_controlled() first")
         p = self._params_pin
         p[0] = self.lam if lam is None else lam
         p[1] = self.dt if dt is None else dt
@@ -315,12 +357,74 @@ class Diffusion2D:
         torch.cuda.current_stream().synchronize()
         return float(self._diag_pin[0]), float(self._diag_pin[1])
 
-    def step_controlled_pair(self, lam: Optional[Sequence[float]] = None, dt: Optional[Sequence[float]] = None):
+    # -- pipelined control loop -------------------------------------------------------------------------------
+    def _ctl_slot(self):
+        if self._ctl_slots is None:
+            self._ctl_slots = [(torch.zeros(8, dtype=torch.float64).pin_memory(),
+                                torch.zeros(4, dtype=torch.float64).pin_memory(), native.DoneEvent())
+                               for _ in range(2)]
+        k = self._ctl_next
+        self._ctl_next = (k + 1) % 2
+        return k, self._ctl_slots[k]
+
+    def _ctl_collect(self):
+        k, pair = self._ctl_pending.pop(0)
+        _, d, ev = self._ctl_slots[k]
+        ev.wait()
+        if pair:
+            return (float(d[0]), float(d[1])), (float(d[2]), float(d[3]))
+        return float(d[0]), float(d[1])
+
+    def _step_controlled_pipelined(self, lam, dt, pair: bool):
+        """Queue one controlled step (or pair), THEN wait for the previous one and return its diagnostic
+        (``None`` on the first call).  Same H2D / D2H traffic per step as the blocking form; the host sees every
+        step's ``(max, sum)`` one submission late, and the GPU never waits for the host."""
+        if not self._running:
+            self.begin()
+        k, (p, d, ev) = self._ctl_slot()
+        if pair:
+            for q in range(2):
+                p[4 * q + 0] = self.lam if lam is None else lam[q]
+                p[4 * q + 1] = self.dt if dt is None else dt[q]
+                p[4 * q + 2] = self._dx
+                p[4 * q + 3] = self._dy
+            push = self.plan.next(self.T2, two_step=True)
+            native.diffusion2d_step2_controlled_submit(self.T2, self.T, self.Cp, p, self._params2_dev,
+                                                       self._diag2_dev, d, ev, push=push,
+                                                       mid=self._mid if push is not None else None)
+            self.steps_done += 2
+        else:
+            p[0] = self.lam if lam is None else lam
+            p[1] = self.dt if dt is None else dt
+            p[2] = self._dx
+            p[3] = self._dy
+            native.diffusion2d_step_controlled_submit(self.T2, self.T, self.Cp, p, self._params_dev, self._diag_dev,
+                                                      d, ev, b_width=self.b_width, push=self.plan.next(self.T2))
+            self.steps_done += 1
+        self.T, self.T2 = self.T2, self.T
+        self._ctl_pending.append((k, pair))
+        if len(self._ctl_pending) > 1:
+            return self._ctl_collect()
+        return None
+
+    def drain_controlled(self):
+        """Wait for every submitted controlled step; returns their diagnostics, oldest first."""
+        out = []
+        while self._ctl_pending:
+            out.append(self._ctl_collect())
+        return out
+
+    def step_controlled_pair(self, lam: Optional[Sequence[float]] = None, dt: Optional[Sequence[float]] = None, *,
+                             pipelined: bool = False):
         """``mode='temporal'``: one end-to-end PAIR of steps.  The host hands over both steps' parameters in pinned
         memory (64 B) and reads back ``((max, sum) after step k+1, (max, sum) after step k+2)`` (32 B); it decides
-        every two steps instead of every step.  Experimental like the mode itself."""
+        every two steps instead of every step.  ``pipelined=True``: as in ``step_controlled``."""
         if self.mode != "temporal":
             raise ValueError("step_controlled_pair needs mode='temporal'")
+        if pipelined:
+            return self._step_controlled_pipelined(lam, dt, pair=True)
+        if self._ctl_pending:
+            raise RuntimeError("pipelined steps are in flight: call drain_controlled() first")
         if not self._running:
             self.begin()
         p = self._params2_pin

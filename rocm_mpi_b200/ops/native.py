@@ -72,6 +72,13 @@ def _declare(lib) -> None:
         "igg_diffusion2d_step": ([vp, vp, vp, i, i, d, d, d, d, C.POINTER(StepOpts), i, i, i, i,
                                  C.POINTER(Push2D), vp], i),
         "igg_diffusion2d_step_controlled": ([vp, vp, vp, i, i, vp, vp, vp, vp, vp, i, i, C.POINTER(Push2D), vp], i),
+        "igg_diffusion2d_step_controlled_submit": ([vp, vp, vp, i, i, vp, vp, vp, vp, vp, i, i, C.POINTER(Push2D), vp,
+                                                   vp], i),
+        "igg_diffusion2d_step2_controlled_submit": ([vp, vp, vp, i, i, vp, vp, vp, vp, vp, C.POINTER(Push2D),
+                                                    C.POINTER(Mid2D), vp, vp], i),
+        "igg_event_create": ([C.POINTER(vp)], i),
+        "igg_event_destroy": ([vp], i),
+        "igg_event_wait": ([vp, i], i),
         "igg_diffusion2d_resident": ([vp, vp, vp, i, i, d, d, d, d, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), vp,
                                      u64, C.POINTER(vp), vp, i, C.POINTER(i), vp], i),
         "igg_diffusion2d_run": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, i, C.POINTER(Push2D), C.POINTER(Push2D), vp], i),
@@ -93,6 +100,7 @@ def _declare(lib) -> None:
         "igg_ipc_close": ([vp], i),
         "igg_can_access_peer": ([i, i, C.POINTER(i)], i),
         "igg_halo_exchange_peer": ([vp, i, C.POINTER(HaloSync), vp], i),
+        "igg_halo_exchange_peer_ex": ([vp, i, C.POINTER(HaloSync), i, vp], i),
         "igg_neighbor_barrier": ([C.POINTER(HaloSync), vp], i),
         "igg_wait_epoch": ([C.POINTER(HaloSync), vp], i),
         "igg_peer_copy": ([vp, vp, sz, vp, u64, vp, vp], i),
@@ -275,6 +283,65 @@ def diffusion2d_step2_controlled(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Te
                                                 _temporal_scratch(T.device).data_ptr(), diag_pin.data_ptr(),
                                                 C.byref(push) if push is not None else None,
                                                 C.byref(mid) if mid is not None else None, _stream()))
+
+
+class DoneEvent:
+    """Completion event of a submitted controlled step (``igg_event_create``): ``wait()`` polls until the step's
+    diagnostic has arrived in its pinned slot."""
+
+    def __init__(self) -> None:
+        h = C.c_void_p()
+        _check(require().igg_event_create(C.byref(h)))
+        self.handle = h.value
+
+    def wait(self, spin: bool = True) -> None:
+        _check(require().igg_event_wait(self.handle, 1 if spin else 0))
+
+    def __del__(self) -> None:
+        try:
+            if self.handle and _lib is not None:
+                _lib.igg_event_destroy(self.handle)
+        except Exception:
+            pass
+        self.handle = None
+
+
+def diffusion2d_step_controlled_submit(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, params_pin: torch.Tensor,
+                                       params_dev: torch.Tensor, diag_dev: torch.Tensor, diag_pin: torch.Tensor,
+                                       done: DoneEvent, b_width: Sequence[int] = (1, 1),
+                                       push: Optional[Push2D] = None) -> None:
+    """``igg_diffusion2d_step_controlled_submit``: queue H2D of the 4 parameters, fused step, D2H of ``[max, sum]``
+    and record ``done``; does not wait.  ``params_pin`` / ``diag_pin`` are the slots of THIS step."""
+    lib = require()
+    nx, ny = T.shape
+    if not (params_pin.is_pinned() and diag_pin.is_pinned()):
+        raise TypeError("params_pin and diag_pin must be pinned host tensors")
+    _check(lib.igg_diffusion2d_step_controlled_submit(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny,
+                                                      params_pin.data_ptr(), _f64(params_dev), _f64(diag_dev),
+                                                      _reduce_scratch(T.device).data_ptr(), diag_pin.data_ptr(),
+                                                      int(b_width[0]), int(b_width[1]),
+                                                      C.byref(push) if push is not None else None, done.handle,
+                                                      _stream()))
+
+
+def diffusion2d_step2_controlled_submit(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, params_pin: torch.Tensor,
+                                        params_dev: torch.Tensor, diag_dev: torch.Tensor, diag_pin: torch.Tensor,
+                                        done: DoneEvent, push: Optional[Push2D] = None,
+                                        mid: Optional["Mid2D"] = None) -> None:
+    """``igg_diffusion2d_step2_controlled_submit``: the pair form of ``diffusion2d_step_controlled_submit``
+    (8 parameters in, 4 diagnostic values out)."""
+    lib = require()
+    nx, ny = T.shape
+    if not (params_pin.is_pinned() and diag_pin.is_pinned()):
+        raise TypeError("params_pin and diag_pin must be pinned host tensors")
+    if params_pin.numel() < 8 or params_dev.numel() < 8 or diag_dev.numel() < 4 or diag_pin.numel() < 4:
+        raise ValueError("need 8 parameter doubles and 4 diagnostic doubles")
+    _check(lib.igg_diffusion2d_step2_controlled_submit(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny,
+                                                       params_pin.data_ptr(), _f64(params_dev), _f64(diag_dev),
+                                                       _temporal_scratch(T.device).data_ptr(), diag_pin.data_ptr(),
+                                                       C.byref(push) if push is not None else None,
+                                                       C.byref(mid) if mid is not None else None, done.handle,
+                                                       _stream()))
 
 
 def diffusion2d_midlines(T: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float, _dy: float,

@@ -76,6 +76,12 @@ class Fabric:
         self._opened: Dict[bytes, int] = {}             # IPC handle -> mapped base pointer
         self._peer_ptrs: Dict[int, Dict[int, int]] = {}  # local data_ptr -> {rank: peer pointer}
         self._keepalive: List[object] = []
+        # strong references to every registered tensor: while a field is registered its storage cannot be freed,
+        # so the caching allocator can never hand the same address to another tensor (a reused address would
+        # look "already registered" on this rank only -> ranks disagree about entering the collective, or
+        # the neighbours keep storing into freed memory)
+        self._registered: Dict[int, torch.Tensor] = {}
+        self._free_banks: List[int] = []
         self.neighbors = neighbor_offsets(g)
         self.neighbor_ranks = sorted({r for _, r in self.neighbors})
         self._next_bank = 0
@@ -119,11 +125,17 @@ class Fabric:
         return t
 
     def register(self, t: torch.Tensor) -> None:
-        """Collective: make ``t`` addressable by the neighbours (no-op if already registered)."""
+        """Collective: make ``t`` addressable by the neighbours (no-op if already registered).
+
+        The fabric keeps ``t`` alive until :meth:`unregister` / :meth:`free` / :meth:`close`: a registration
+        is a promise to the neighbours that the address stays valid.  Register long-lived fields (the
+        solvers allocate theirs with :func:`fabric_zeros`), not per-step temporaries; every rank must
+        register the same fields in the same order."""
         key = t.data_ptr()
         if key in self._peer_ptrs:
             return
         g = self.g
+        self._registered[key] = t
         if g.nprocs == 1:
             self._peer_ptrs[key] = {0: key}
             return
@@ -152,6 +164,30 @@ class Fabric:
             ptrs[r] = base + o
         self._peer_ptrs[key] = ptrs
 
+    def unregister(self, t: torch.Tensor) -> None:
+        """Collective: drop the registration of ``t`` (all ranks, same order); the neighbours' mappings of
+        its allocation are closed when no other registered field shares it."""
+        key = t.data_ptr()
+        if key not in self._peer_ptrs:
+            return
+        torch.cuda.synchronize()
+        self.g.comm.barrier()                       # no kernel anywhere still stores into it
+        mine = self._handles.pop(key, {})
+        self._peer_ptrs.pop(key, None)
+        self._registered.pop(key, None)
+        still = {h for hs in self._handles.values() for h in hs.values()}
+        for h in set(mine.values()) - still:
+            base = self._opened.pop(h, None)
+            if base is not None:
+                self.lib.igg_ipc_close(base)
+        self._forget_tables(key)
+        self.g.comm.barrier()
+
+    def _forget_tables(self, data_ptr: int) -> None:
+        eng = self.g.cache.get(("halo", "peer"))
+        if eng is not None:
+            eng.forget(data_ptr)
+
     def is_registered(self, t: torch.Tensor) -> bool:
         return t.data_ptr() in self._peer_ptrs
 
@@ -160,11 +196,37 @@ class Fabric:
 
     # -- flag banks -----------------------------------------------------------------------------
     def new_bank(self) -> int:
+        """Collective by convention: every rank takes (and releases) banks in the same order."""
+        if self._free_banks:
+            return self._free_banks.pop()
         if self._next_bank >= native.FLAG_BANKS:
-            raise RuntimeError("out of flag banks")
+            raise RuntimeError("out of flag banks (32 per grid): close() solvers / plans that are no longer used")
         b = self._next_bank
         self._next_bank += 1
         return b
+
+    def release_bank(self, bank: int) -> None:
+        """Collective: return ``bank`` to the free list with all its flags and counters cleared."""
+        torch.cuda.synchronize()
+        self.g.comm.barrier()                       # no neighbour is still signalling into it
+        b = bank * native.BANK_STRIDE
+        self.flag_pad[b:b + native.BANK_STRIDE].zero_()
+        self.count_pad[b:b + native.BANK_STRIDE].zero_()
+        torch.cuda.synchronize()
+        self.g.comm.barrier()
+        self._free_banks.append(bank)
+
+    def check_all_errors(self) -> None:
+        """Synchronise and raise if a flag wait on ANY bank timed out (called from ``toc``, ``gather`` and
+        ``finalize_global_grid`` so that no application path can miss a stale halo)."""
+        torch.cuda.current_stream().synchronize()
+        words = self.flag_pad.view(native.FLAG_BANKS, native.BANK_STRIDE)[:, native.SLOT_ERR]
+        bad = torch.nonzero(words).flatten().tolist()
+        if bad:
+            v = int(words[bad[0]].item())
+            words[bad] = 0
+            raise RuntimeError(f"peer flag wait timed out on bank(s) {bad} (word {v & ((1 << 63) - 1)}); "
+                               "a neighbour did not reach the matching call -- halo contents are stale")
 
     def bank_ptr(self, bank: int, rank: Optional[int] = None) -> int:
         base = self.flag_pad.data_ptr() if rank is None else self.peer_ptr(self.flag_pad, rank)
@@ -205,6 +267,8 @@ class Fabric:
             if base is not None:
                 self.lib.igg_ipc_close(base)
         self._peer_ptrs.pop(key, None)
+        self._registered.pop(key, None)
+        self._forget_tables(key)
         self.g.comm.barrier()                       # nobody maps the block any more
         native._check(self.lib.igg_fabric_free(key))
         del self._owned[key]
@@ -220,6 +284,7 @@ class Fabric:
         self._opened.clear()
         self._peer_ptrs.clear()
         self._handles.clear()
+        self._registered.clear()
         self.g.comm.barrier()                       # every rank has dropped its mappings
         for ptr in list(self._owned):
             self.lib.igg_fabric_free(ptr)
@@ -245,12 +310,14 @@ def fabric_zeros(shape: Sequence[int], dtype: torch.dtype = torch.float64) -> to
 class PeerHalo:
     """``update_halo`` over peer memory: one kernel launch per call (transport ``peer``)."""
 
+    CHECK_EVERY = 256        # launches between two host-side looks at the error word
+
     def __init__(self, g: GlobalGrid) -> None:
         self.g = g
         self.fab = get_fabric(g)
         self.bank = self.fab.new_bank()
         self.epoch = 0
-        self._tables: Dict[tuple, Tuple[torch.Tensor, int]] = {}
+        self._tables: Dict[tuple, Tuple[torch.Tensor, int, int]] = {}
         self.launches = 0
 
     def _boxes(self, A: torch.Tensor):
@@ -285,25 +352,47 @@ class PeerHalo:
                 x.elem_bytes = A.element_size()
                 xf.append(x)
         n = len(xf)
+        if n > 27 * native.MAX_HALO_FIELDS:
+            raise ValueError(f"update_halo(peer): too many boxes in one call ({n}); pass at most "
+                             f"{native.MAX_HALO_FIELDS} fields")
+        # CTAs of the exchange kernel: one per 1024 copy units (16-byte vectors for contiguous runs, single
+        # elements for strided planes) -- the grid follows the bytes moved, not the machine size
+        units = 0
+        for x in xf:
+            rows, run, eb = x.extent[0] * x.extent[1], x.extent[2], x.elem_bytes
+            vec = run * eb >= 64 and x.src_start[2] == x.dst_start[2] and (x.n[2] * eb) % 16 == 0
+            units += rows * (1 + run * eb // 16 if vec else run)
+        ctas = max(1, -(-units // 1024))
         if n:
             arr = (native.HaloXfer * n)(*xf)
             host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
             dev = host.to(self.g.device)
         else:
             dev = torch.zeros(16, dtype=torch.uint8, device=self.g.device)
-        self._tables[key] = (dev, n)
+        self._tables[key] = (dev, n, ctas)
         if len(self._tables) > 64:
             self._tables.pop(next(iter(self._tables)))
-        return dev, n
+        return dev, n, ctas
 
     def update(self, fields: Sequence[torch.Tensor]) -> None:
-        dev, n = self._table(fields)
+        dev, n, ctas = self._table(fields)
         if not self.fab.neighbors:
             return
         self.epoch += 1
         sync = self.fab.sync_struct(self.bank, self.epoch)
-        native._check(self.fab.lib.igg_halo_exchange_peer(dev.data_ptr(), n, C.byref(sync), native._stream()))
+        native._check(self.fab.lib.igg_halo_exchange_peer_ex(dev.data_ptr(), n, C.byref(sync), ctas,
+                                                             native._stream()))
         self.launches += 1
+        if self.launches % self.CHECK_EVERY == 0:
+            # a flag wait that timed out leaves the halo stale (the kernel then stores nothing): do not let a
+            # long loop run on silently -- the host looks at the error word now and then, and at every
+            # toc() / gather() / finalize_global_grid()
+            self.fab.check_errors(self.bank)
+
+    def forget(self, data_ptr: int) -> None:
+        """Drop cached transfer tables that mention the field at ``data_ptr`` (its registration ended)."""
+        for key in [k for k in self._tables if any(f[0] == data_ptr for f in k)]:
+            del self._tables[key]
 
     def close(self) -> None:
         self._tables.clear()
@@ -417,6 +506,18 @@ class PushPlan:
         d = (self._desc2 if two_step else self._desc)[dst.data_ptr()]
         d.epoch = self.epoch
         return d
+
+    def close(self) -> None:
+        """Collective: give the flag bank (and the mid-line buffer) back; the plan is unusable afterwards."""
+        if self.bank is None:
+            return
+        if self._active:
+            self.finish()
+        if getattr(self, "_mid_buf", None) is not None:
+            self.fab.free(self._mid_buf)
+            self._mid_buf = None
+        self.fab.release_bank(self.bank)
+        self.bank = None
 
     def finish(self, check: bool = True) -> None:
         """Wait until every neighbour's pushes of the last epoch have landed here."""

@@ -32,6 +32,9 @@ def gather(A_local: torch.Tensor, A_global: Optional[torch.Tensor], root: int = 
     ``Array(T[2:end-1,2:end-1])`` (``scripts/diffusion_2D_ap.jl:45``).
     """
     g = global_grid()
+    fab = g.cache.get("fabric")
+    if fab is not None:
+        fab.check_all_errors()              # never gather a field whose halo exchange timed out
     block = A_local.detach()
     if block.is_cuda:
         block = block.contiguous().cpu()

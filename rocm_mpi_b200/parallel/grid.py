@@ -192,6 +192,13 @@ def finalize_global_grid(*, finalize_dist: bool = True) -> None:
     """
     global _GRID
     g = global_grid()
+    fab = g.cache.get("fabric")
+    pending = None
+    if fab is not None:
+        try:
+            fab.check_all_errors()
+        except RuntimeError as e:           # still release everything, then report
+            pending = e
     for key, obj in list(g.cache.items()):
         close = getattr(obj, "close", None)
         if callable(close):
@@ -200,6 +207,8 @@ def finalize_global_grid(*, finalize_dist: bool = True) -> None:
     if finalize_dist:
         g.comm.finalize()
     _GRID = None
+    if pending is not None:
+        raise pending
 
 
 def _n_g(dim: int, A=None) -> int:

@@ -49,7 +49,11 @@ class DeviceTimer:
         else:
             dt = time.perf_counter() - self._t0
         if grid_is_initialized():
-            dt = global_grid().comm.allreduce_max(dt)
+            g = global_grid()
+            fab = g.cache.get("fabric")
+            if fab is not None:
+                fab.check_all_errors()      # a timed-out flag wait must not go unnoticed past a timing point
+            dt = g.comm.allreduce_max(dt)
         return dt
 
 

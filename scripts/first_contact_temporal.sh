@@ -8,16 +8,16 @@ cd "$REPO" || exit 1
 OUT=gpurun_out
 mkdir -p $OUT
 echo "== stage 1: numerics (kernel alone, solver with self-neighbour, controlled pairs)" | tee $OUT/t2_summary.txt
-timeout 600 python scripts/check_temporal.py --skip-timing > $OUT/t2_check.log 2>&1
+timeout 300 python scripts/check_temporal.py --skip-timing > $OUT/t2_check.log 2>&1
 rc=$?; echo "check_temporal rc=$rc" | tee -a $OUT/t2_summary.txt; tail -n 25 $OUT/t2_check.log
 echo "== stage 2: staged pytest tier" | tee -a $OUT/t2_summary.txt
-timeout 900 python -m pytest tests -m "temporal_gpu or staged_gpu" -q > $OUT/t2_pytest.log 2>&1
+timeout 400 python -m pytest tests/test_temporal_gpu.py tests/test_hide_drivers_gpu.py -m gpu -q > $OUT/t2_pytest.log 2>&1
 echo "pytest rc=$?" | tee -a $OUT/t2_summary.txt; tail -n 5 $OUT/t2_pytest.log | tee -a $OUT/t2_summary.txt
 if [ $rc -eq 0 ]; then
   echo "== stage 3: timing at 16384^2, fused vs temporal" | tee -a $OUT/t2_summary.txt
   timeout 300 python scripts/check_temporal.py --timing-only 2>&1 | tee -a $OUT/t2_summary.txt
   echo "== stage 4: sweep" | tee -a $OUT/t2_summary.txt
-  timeout 1500 bash scripts/sweep_temporal.sh 16384 16384 30 >> $OUT/t2_summary.txt 2>&1
+  timeout 600 bash scripts/sweep_temporal.sh 16384 16384 30 >> $OUT/t2_summary.txt 2>&1
   echo "== stage 5: bench line (value + pair-controlled e2e)" | tee -a $OUT/t2_summary.txt
   timeout 300 python bench.py --impl temporal --steps 50 --warmup 10 2>&1 | tail -n 1 | tee $OUT/bench_temporal_1gpu.json
 fi

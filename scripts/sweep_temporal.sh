@@ -11,7 +11,7 @@ for srb in 16 8; do
  for rpt in 2 4; do
   for rows in 124 252 508; do
     echo "== IGG_T2_SRB=$srb IGG_T2_RPT=$rpt IGG_T2_ROWS=$rows" | tee -a "$OUT"
-    IGG_T2_SRB=$srb IGG_T2_RPT=$rpt IGG_T2_ROWS=$rows timeout 300 python "$REPO/scripts/check_temporal.py" \
+    IGG_T2_SRB=$srb IGG_T2_RPT=$rpt IGG_T2_ROWS=$rows timeout 120 python "$REPO/scripts/check_temporal.py" \
         --nx "$NX" --ny "$NY" --steps "$STEPS" --timing-only 2>&1 | grep -E "ms/step|MISMATCH|rror" | tee -a "$OUT"
   done
  done

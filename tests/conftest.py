@@ -11,10 +11,6 @@ if ROOT not in sys.path:
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: test needs a CUDA device (run on the B200 box with -m gpu)")
     config.addinivalue_line("markers", "multigpu: test needs >= 2 CUDA devices")
-    config.addinivalue_line("markers", "temporal_gpu: staged GPU tests of the two-steps-per-pass kernel "
-                            "(not part of the gpu tier until the kernel has run on hardware)")
-    config.addinivalue_line("markers", "staged_gpu: GPU tests of drivers composed from GPU-tested kernels that have "
-                            "not themselves run on hardware yet (not part of the gpu tier)")
 
 
 @pytest.fixture(scope="session", autouse=True)

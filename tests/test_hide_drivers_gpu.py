@@ -1,5 +1,5 @@
-"""GPU tests of drivers that were composed from GPU-tested kernels AFTER the round's GPU budget was spent --
-STAGED under the marker ``staged_gpu`` (not ``gpu``) until they have passed once on a B200 box:
+"""GPU tests of the drivers composed from the frame / interior kernels (``gpu`` tier; they first passed on a B200 in
+round 2, ``gpurun_out/t2_pytest.log``):
 
 * ``Diffusion3D(mode="hide")``: frame kernel + push on a high-priority stream, interior kernel on a low-priority one;
 * ``Diffusion2D(mode="hide_exchange")``: the reference's commented variant (3), ``scripts/diffusion_2D_perf_hide.jl:94-101``
@@ -10,7 +10,7 @@ import torch
 
 import rocm_mpi_b200 as igg
 
-pytestmark = [pytest.mark.staged_gpu,
+pytestmark = [pytest.mark.gpu,
               pytest.mark.skipif(not torch.cuda.is_available(), reason="needs a CUDA device")]
 TOL = 1e-12
 

@@ -1,6 +1,6 @@
-"""GPU tests of the two-steps-per-pass kernel -- STAGED: marked ``temporal_gpu``, not ``gpu``, because the kernel
-has not run on hardware yet (the ``gpu`` tier must stay green).  First contact: ``scripts/check_temporal.py``;
-then ``python -m pytest tests -m temporal_gpu`` on a B200 box, and re-mark as ``gpu`` once they pass.
+"""GPU tests of the two-steps-per-pass kernel (``csrc/temporal2d.cu``).  Part of the ``gpu`` tier since the kernel
+passed its first run on a B200 (``gpurun_out/t2_check.log``: bit-identical to two one-step launches without
+neighbours, <= 1.2e-16 through the solver with a self-neighbour).
 
 Each test compares against two launches of the GPU-tested one-step kernel (same arithmetic, same FMA
 contraction), which itself is tested against the PyTorch fp32/fp64 statement in ``tests/test_kernels_gpu.py``.
@@ -12,7 +12,7 @@ import rocm_mpi_b200 as igg
 from rocm_mpi_b200.ops import native
 from rocm_mpi_b200.ops import reference as ref
 
-pytestmark = [pytest.mark.temporal_gpu,
+pytestmark = [pytest.mark.gpu,
               pytest.mark.skipif(not torch.cuda.is_available(), reason="needs a CUDA device")]
 TOL = 1e-12
 PH = (1.3, 1e-3, 2.0, 3.0)
