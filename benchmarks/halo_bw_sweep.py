@@ -35,6 +35,7 @@ def main() -> int:
     ap.add_argument("--min-kb", type=int, default=4)
     ap.add_argument("--max-mb", type=int, default=256)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--label", default="", help="free text stored with the result (e.g. the NCCL_* settings of this run)")
     a = ap.parse_args()
     me, dims, nprocs, _, _ = igg.init_global_grid(4, 4, 1, dimy=1, periodx=1, quiet=True)
     g = igg.global_grid()
@@ -43,7 +44,8 @@ def main() -> int:
     dst, src = (me + 1) % nprocs, (me - 1) % nprocs
     max_bytes = a.max_mb << 20
     recv = fab.zeros((max_bytes // 8,))
-    send = torch.rand(max_bytes // 8, dtype=torch.float64, device=g.device)
+    ramp = (torch.arange(max_bytes // 8, device=g.device) % 4093).to(torch.float64)
+    send = ramp + float(me)             # the receiver knows what its predecessor sends: ramp + src
     flag = fab.zeros((2,), torch.int64)
     cnt = torch.zeros(1, dtype=torch.int64, device=g.device)
     recv_n = torch.empty_like(send)
@@ -82,14 +84,20 @@ def main() -> int:
             res[tr + "_GBps"] = round(size / (ms * 1e-3) / 1e9, 2)
         if tr == "peer" and int(flag[1]) != 0:
             raise RuntimeError("peer flag wait timed out")
-        ok = bool(torch.equal(recv[: size // 8], send[: size // 8])) if nprocs == 1 else True
-        res["ok"] = ok
+        # both arms are checked on every rank against what the ring predecessor sent
+        n = size // 8
+        want = ramp[:n] + float(src)
+        ok = bool(torch.equal(recv[:n], want)) and bool(torch.equal(recv_n[:n], want))
+        res["ok"] = bool(g.comm.allreduce_max(0.0 if ok else 1.0) == 0.0)
+        recv[:n].zero_()
+        recv_n[:n].zero_()
         rows.append(res)
         if me == 0:
             print(json.dumps(res), flush=True)
         size *= 4
     if me == 0:
-        summary = {"bench": "halo_bw_sweep", "n_gpus": nprocs, "nvlink_ref_GBps": {"measured_peer_copy": 770, "nominal": 900},
+        summary = {"bench": "halo_bw_sweep", "n_gpus": nprocs, "label": a.label,
+                   "nccl_env": {k: v for k, v in os.environ.items() if k.startswith("NCCL_")}, "nvlink_ref_GBps": {"measured_peer_copy": 770, "nominal": 900},
                    "rows": rows}
         if a.out:
             os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)

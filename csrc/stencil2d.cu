@@ -128,6 +128,62 @@ __device__ __forceinline__ void consumer_sync(int nthreads) {
     asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
 }
 
+// Fused diagnostic {max, sum}, shared by the tile and the strip kernel: every consumer thread brings its partial;
+// CTA partial -> scratch, the last CTA (ticket) folds all partials in a fixed order (deterministic sum) and
+// re-arms the ticket.  The hot loops fold with fmax (one instruction, drops NaN); a NaN anywhere makes the SUM
+// NaN, and then the max is reported as NaN too -- what the reference's maximum(T_v) would show
+// (scripts/diffusion_2D_perf_hide.jl:115).
+template <int CONSUMERS>
+__device__ __forceinline__ void diag_finish(DiagScratch* scratch, double* diag_out, double dmax, double dsum) {
+    constexpr int NCW = CONSUMERS / 32;
+    const int tid = threadIdx.x;
+    __shared__ double red[64];
+    __shared__ bool is_last;
+    auto block_fold = [&](double& mx, double& sm) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+            sm += __shfl_xor_sync(0xffffffffu, sm, off);
+        }
+        if ((tid & 31) == 0) { red[tid >> 5] = mx; red[32 + (tid >> 5)] = sm; }
+        consumer_sync(CONSUMERS);
+        if (tid < 32) {
+            mx = tid < NCW ? red[tid] : -INFINITY;
+            sm = tid < NCW ? red[32 + tid] : 0.0;
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                sm += __shfl_xor_sync(0xffffffffu, sm, off);
+            }
+        }
+        consumer_sync(CONSUMERS);
+    };
+    block_fold(dmax, dsum);
+    if (tid == 0) {
+        scratch->pmax[blockIdx.x] = dmax;
+        scratch->psum[blockIdx.x] = dsum;
+        __threadfence();
+        is_last = atomicAdd(&scratch->ticket, 1u) == gridDim.x - 1;
+    }
+    consumer_sync(CONSUMERS);
+    if (is_last) {
+        __threadfence();
+        dmax = -INFINITY;
+        dsum = 0.0;
+        for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS) {
+            dmax = fmax(dmax, scratch->pmax[b2]);
+            dsum += scratch->psum[b2];
+        }
+        block_fold(dmax, dsum);
+        if (tid == 0) {
+            diag_out[0] = dsum != dsum ? dsum : dmax;
+            diag_out[1] = dsum;
+            scratch->ticket = 0;
+        }
+    }
+}
+
+
 // ------------------------------------------------------------------------------------------------
 // variant 1: persistent, warp-specialised, TMA + mbarrier pipeline
 // ------------------------------------------------------------------------------------------------
@@ -238,8 +294,8 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
                 if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
             }
             if (diag) {
-                if (wA) { dmax = igg::max_nan(dmax, vA); dsum += vA; }
-                if (wB) { dmax = igg::max_nan(dmax, vB); dsum += vB; }
+                if (wA) { dmax = fmax(dmax, vA); dsum += vA; }
+                if (wB) { dmax = fmax(dmax, vB); dsum += vB; }
             }
             a = b;
             b = c;
@@ -254,52 +310,7 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
     }
 
     // fused diagnostic: CTA partial -> scratch, last CTA (ticket) folds all partials in a fixed order
-    if (diag) {
-        __shared__ double red[64];
-        __shared__ bool is_last;
-        auto block_fold = [&](double& mx, double& sm) {
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-                sm += __shfl_xor_sync(0xffffffffu, sm, off);
-            }
-            if ((tid & 31) == 0) { red[tid >> 5] = mx; red[32 + (tid >> 5)] = sm; }
-            consumer_sync(CONSUMERS);
-            if (tid < 32) {
-                mx = tid < NCW ? red[tid] : -INFINITY;
-                sm = tid < NCW ? red[32 + tid] : 0.0;
-#pragma unroll
-                for (int off = 16; off > 0; off >>= 1) {
-                    mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-                    sm += __shfl_xor_sync(0xffffffffu, sm, off);
-                }
-            }
-            consumer_sync(CONSUMERS);
-        };
-        block_fold(dmax, dsum);
-        if (tid == 0) {
-            p.diag->pmax[blockIdx.x] = dmax;
-            p.diag->psum[blockIdx.x] = dsum;
-            __threadfence();
-            is_last = atomicAdd(&p.diag->ticket, 1u) == gridDim.x - 1;
-        }
-        consumer_sync(CONSUMERS);
-        if (is_last) {
-            __threadfence();
-            dmax = -INFINITY;
-            dsum = 0.0;
-            for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS) {
-                dmax = igg::max_nan(dmax, p.diag->pmax[b2]);
-                dsum += p.diag->psum[b2];
-            }
-            block_fold(dmax, dsum);
-            if (tid == 0) {
-                p.diag_out[0] = dmax;
-                p.diag_out[1] = dsum;
-                p.diag->ticket = 0;
-            }
-        }
-    }
+    if (diag) diag_finish<CONSUMERS>(p.diag, p.diag_out, dmax, dsum);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -464,8 +475,8 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
                     if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
                 }
                 if (diag) {
-                    if (wA) { dmax = igg::max_nan(dmax, vA); dsum += vA; }
-                    if (wB) { dmax = igg::max_nan(dmax, vB); dsum += vB; }
+                    if (wA) { dmax = fmax(dmax, vA); dsum += vA; }
+                    if (wB) { dmax = fmax(dmax, vB); dsum += vB; }
                 }
                 a = bb;
                 bb = c;
@@ -490,52 +501,7 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
         }
     }
 
-    if (diag) {
-        __shared__ double red[64];
-        __shared__ bool is_last;
-        auto block_fold = [&](double& mx, double& sm) {
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-                sm += __shfl_xor_sync(0xffffffffu, sm, off);
-            }
-            if ((tid & 31) == 0) { red[tid >> 5] = mx; red[32 + (tid >> 5)] = sm; }
-            consumer_sync(CONSUMERS);
-            if (tid < 32) {
-                mx = tid < NCW ? red[tid] : -INFINITY;
-                sm = tid < NCW ? red[32 + tid] : 0.0;
-#pragma unroll
-                for (int off = 16; off > 0; off >>= 1) {
-                    mx = igg::max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-                    sm += __shfl_xor_sync(0xffffffffu, sm, off);
-                }
-            }
-            consumer_sync(CONSUMERS);
-        };
-        block_fold(dmax, dsum);
-        if (tid == 0) {
-            p.diag->pmax[blockIdx.x] = dmax;
-            p.diag->psum[blockIdx.x] = dsum;
-            __threadfence();
-            is_last = atomicAdd(&p.diag->ticket, 1u) == gridDim.x - 1;
-        }
-        consumer_sync(CONSUMERS);
-        if (is_last) {
-            __threadfence();
-            dmax = -INFINITY;
-            dsum = 0.0;
-            for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS) {
-                dmax = igg::max_nan(dmax, p.diag->pmax[b2]);
-                dsum += p.diag->psum[b2];
-            }
-            block_fold(dmax, dsum);
-            if (tid == 0) {
-                p.diag_out[0] = dmax;
-                p.diag_out[1] = dsum;
-                p.diag->ticket = 0;
-            }
-        }
-    }
+    if (diag) diag_finish<CONSUMERS>(p.diag, p.diag_out, dmax, dsum);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -51,6 +51,7 @@ struct T2Params {
     MidLines ml;
     const uint64_t* mid_flag[4];   // my mid flags, one per line (xlo, xhi, ylo, yhi); NULL = no neighbour
     int has_push;
+    int lean;                      // 1: inner items take the lean path (IGG_T2_LEAN=0 switches it off for A/B runs)
     int edge_tiles[9];
     int side_nb[4];
     igg_push2d push;
@@ -63,8 +64,150 @@ __device__ __forceinline__ void consumer_sync_(int nthreads) {
     asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
 }
 
-template <int SRB, int RPT>
-__global__ void __launch_bounds__(NPAIR*(SRB / RPT) + 32, SRB == 8 ? 2 : 1)
+// ---- lean path for items whose whole box lies inside the updated region (all but the items on the array edge) ----
+// Same arithmetic and the same ring / barrier protocol as the generic path below (step1_rows / step2_rows of
+// temporal2d_core.h), but written against 32-bit shared-memory addresses that are advanced incrementally: a
+// thread's row and column offsets never change, so per block only the three slot bases move.  The generic path
+// spends ~430 instructions per thread and block of which 100 are FP64 (ncu, profiles/ncu_temporal2_r2a.md); this one
+// has no boundary rules, no pushes, no per-row pointer selection and no divisions.
+__device__ __forceinline__ d2 lds128(uint32_t a) {
+    d2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ double lds64(uint32_t a) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, double x, double y) {
+    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(x), "d"(y) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@!p bra WAIT_%=;\n\t}"
+        ::"r"(bar), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_u32(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+struct T2Acc {            // running diagnostics of a thread
+    double d1max, d1sum, d2max, d2sum;
+};
+
+template <int SRB, int RPT, bool DIAG>
+__device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict__ T2, int ny, const Phys& ph1,
+                                              const Phys& ph2, uint32_t sT, uint32_t sC, uint32_t sM, uint32_t fullT,
+                                              uint32_t emptyT, uint32_t fullC, uint32_t emptyC, unsigned tq, unsigned cq,
+                                              unsigned mq, int cp, int rg, int consumers, T2Acc& acc) {
+    constexpr int NRG = SRB / RPT;
+    constexpr uint32_t ROWB = BW * 8, BLKB = SRB * ROWB;
+    const uint32_t colB = (uint32_t)cp * 16u;
+    const uint32_t myB = (uint32_t)(rg * RPT) * ROWB + colB;      // my first row, my column pair, inside a block
+    const bool lane0 = (threadIdx.x & 31) == 0;
+    const bool pair_ok = cp >= 1 && cp <= NPAIR - 2;
+    const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;
+    // slots and parities of block 0
+    uint32_t ts = tq % SNT, tph = (tq / SNT) & 1u;
+    uint32_t cs = cq % SNC, cph = (cq / SNC) & 1u;
+    uint32_t ms = mq % SNM;
+    uint32_t tprev = ts, cprev = cs, mprev = (ms + SNM - 1) % SNM;
+    mbar_wait_u32(fullT + ts * 8, tph);
+    // output pointer of my first step-2 row of block 0 (rows xb - 1 + rg*RPT + r)
+    int x = it.xin0 - 1 + rg * RPT;
+    double* out = T2 + (size_t)x * ny + (it.yb + 2 * cp);
+    for (int b = 0; b < it.nbi; ++b) {
+        const uint32_t tn = (ts + 1) & (SNT - 1);
+        const uint32_t tnph = tn == 0 ? tph ^ 1u : tph;
+        const bool has_next = b + 1 < it.nbi;
+        if (has_next) mbar_wait_u32(fullT + tn * 8, tnph);
+        mbar_wait_u32(fullC + cs * 8, cph);
+        const uint32_t tc = sT + ts * BLKB, tp = sT + tprev * BLKB, tnx = sT + (has_next ? tn : ts) * BLKB;
+        const uint32_t cc_ = sC + cs * BLKB, cpv = sC + cprev * BLKB;
+        const uint32_t mc = sM + ms * BLKB, mp = sM + mprev * BLKB;
+        // ---- step 1: mid rows rg*RPT ... rg*RPT+RPT-1 of block b
+        {
+            const uint32_t pb = tc + myB;
+            d2 a = lds128(rg == 0 ? tp + (SRB - 1) * ROWB + colB : pb - ROWB);
+            d2 bb = lds128(pb);
+            const uint32_t plast = rg == NRG - 1 ? tnx + colB : pb + RPT * ROWB;
+#pragma unroll
+            for (int r = 0; r < RPT; ++r) {
+                const d2 c = lds128(r + 1 < RPT ? pb + (r + 1) * ROWB : plast);
+                const double bl = lds64(pb + r * ROWB - 8);
+                const double br = lds64(pb + r * ROWB + 16);
+                const d2 cc = lds128(cc_ + myB + r * ROWB);
+                const double mA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph1);
+                const double mB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph1);
+                sts128(mc + myB + r * ROWB, mA, mB);
+                if (DIAG) {
+                    const int xr = x + 1 + r;          // global row of this mid value
+                    if (pair_ok && xr >= x_lo && xr <= x_hi) {
+                        acc.d1max = fmax(fmax(acc.d1max, mA), mB);
+                        acc.d1sum += mA;
+                        acc.d1sum += mB;
+                    }
+                }
+                a = bb;
+                bb = c;
+            }
+        }
+        __syncwarp();
+        if (lane0 && b > 0) mbar_arrive_u32(emptyT + tprev * 8);      // T block b-1 is done
+        consumer_sync_(consumers);                                   // mid block b complete
+        // ---- step 2: output rows xb - 1 + rg*RPT + r from mid rows (rg*RPT - 2 + r) ... (rg*RPT + r)
+        {
+            const uint32_t m0 = mc + myB;                                      // mid row rg*RPT of block b
+            const uint32_t mm1 = rg == 0 ? mp + (SRB - 1) * ROWB + colB : m0 - ROWB;       // row rg*RPT - 1
+            const uint32_t mm2 = rg == 0 ? mp + (SRB - 2) * ROWB + colB : m0 - 2 * ROWB;   // row rg*RPT - 2
+            const uint32_t cm1 = rg == 0 ? cpv + (SRB - 1) * ROWB + colB : cc_ + myB - ROWB;
+            d2 a = lds128(mm2);
+            d2 bb = lds128(mm1);
+#pragma unroll
+            for (int r = 0; r < RPT; ++r) {
+                const uint32_t rc = r == 0 ? mm1 : m0 + (r - 1) * ROWB;        // row of the output cell
+                const d2 c = lds128(m0 + r * ROWB);
+                const double bl = lds64(rc - 8);
+                const double br = lds64(rc + 16);
+                const d2 cc = lds128(r == 0 ? cm1 : cc_ + myB + (r - 1) * ROWB);
+                const double oA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph2);
+                const double oB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph2);
+                const int xr = x + r;
+                if (pair_ok && xr >= x_lo && xr <= x_hi) {
+                    st_cs_f64x2(out + (size_t)r * ny, oA, oB);
+                    if (DIAG) {
+                        acc.d2max = fmax(fmax(acc.d2max, oA), oB);
+                        acc.d2sum += oA;
+                        acc.d2sum += oB;
+                    }
+                }
+                a = bb;
+                bb = c;
+            }
+        }
+        __syncwarp();
+        if (lane0 && b > 0) mbar_arrive_u32(emptyC + cprev * 8);      // Cp block b-1 is done
+        // advance the rings
+        tprev = ts; ts = tn; tph = tnph;
+        cprev = cs; cs = cs + 1 == SNC ? 0 : cs + 1; cph = cs == 0 ? cph ^ 1u : cph;
+        mprev = ms; ms = ms + 1 == SNM ? 0 : ms + 1;
+        x += SRB;
+        out += (size_t)SRB * ny;
+    }
+    __syncwarp();
+    if (lane0) {
+        mbar_arrive_u32(emptyT + tprev * 8);
+        mbar_arrive_u32(emptyC + cprev * 8);
+    }
+}
+
+template <int SRB, int RPT, bool DIAG>
+__global__ void __launch_bounds__(NPAIR*(SRB / RPT) + 32, SRB == 4 ? 4 : (SRB == 8 ? 2 : 1))
 diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapC,
                         const __grid_constant__ T2Params p) {
     constexpr int CONSUMERS = NPAIR * (SRB / RPT);
@@ -139,9 +282,12 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         ph1.lam = p.dev_params[0]; ph1.dt = p.dev_params[1]; ph1._dx = p.dev_params[2]; ph1._dy = p.dev_params[3];
         ph2.lam = p.dev_params[4]; ph2.dt = p.dev_params[5]; ph2._dx = p.dev_params[6]; ph2._dy = p.dev_params[7];
     }
-    const bool diag = p.diag_out != nullptr;
+    constexpr bool diag = DIAG;
     double d1max = -INFINITY, d1sum = 0.0, d2max = -INFINITY, d2sum = 0.0;
     unsigned tq = 0, cq = 0, mq = 0;
+    const uint32_t sT = smem_u32(ringT), sC = smem_u32(ringC), sM = smem_u32(ringM);
+    const uint32_t aFullT = smem_u32(fullT), aEmptyT = smem_u32(emptyT), aFullC = smem_u32(fullC),
+                   aEmptyC = smem_u32(emptyC);
 
     for (int k = 0; k < n_my; ++k) {
         const Item it = make_item(p.g, first + k * gridDim.x);
@@ -150,6 +296,16 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         const bool edge_tile = p.has_push && (e_xl || e_xh || e_yl || e_yh);
         const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;      // inside [1, nx-2] by construction
         const bool inner = item_is_inner(p.g, it);
+        if (inner && p.lean) {
+            T2Acc acc = {d1max, d1sum, d2max, d2sum};
+            t2_inner_item<SRB, RPT, DIAG>(it, p.T2, ny, ph1, ph2, sT, sC, sM, aFullT, aEmptyT, aFullC, aEmptyC, tq, cq,
+                                          mq, cp, rg, CONSUMERS, acc);
+            d1max = acc.d1max; d1sum = acc.d1sum; d2max = acc.d2max; d2sum = acc.d2sum;
+            tq += it.nbi;
+            cq += it.nbi;
+            mq += it.nbi;
+            continue;
+        }
         const int y = it.yb + 2 * cp;
         mbar_wait(&fullT[tq % SNT], (tq / SNT) & 1);
         for (int b = 0; b < it.nbi; ++b) {
@@ -166,8 +322,8 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                 step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, ny, wA, wB);
 #pragma unroll
                 for (int r = 0; r < RPT; ++r) {
-                    if ((wA >> r) & 1u) { d1max = igg::max_nan(d1max, oA[r]); d1sum += oA[r]; }
-                    if ((wB >> r) & 1u) { d1max = igg::max_nan(d1max, oB[r]); d1sum += oB[r]; }
+                    if ((wA >> r) & 1u) { d1max = fmax(d1max, oA[r]); d1sum += oA[r]; }
+                    if ((wB >> r) & 1u) { d1max = fmax(d1max, oB[r]); d1sum += oB[r]; }
                 }
             }
             __syncwarp();
@@ -192,8 +348,8 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                         if (c) push_cell_2d(p.push, nx, ny, x, y + 1, oB[r]);
                     }
                     if (diag) {
-                        if (a) { d2max = igg::max_nan(d2max, oA[r]); d2sum += oA[r]; }
-                        if (c) { d2max = igg::max_nan(d2max, oB[r]); d2sum += oB[r]; }
+                        if (a) { d2max = fmax(d2max, oA[r]); d2sum += oA[r]; }
+                        if (c) { d2max = fmax(d2max, oB[r]); d2sum += oB[r]; }
                     }
                 }
             }
@@ -260,6 +416,10 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                 }
             block_fold();
             if (tid == 0) {
+                // the hot loops fold with fmax (one instruction; it drops NaN): a NaN anywhere makes the SUM NaN,
+                // and then the max is reported as NaN too, like the reference's maximum(T_v)
+                if (v[1] != v[1]) v[0] = v[1];
+                if (v[3] != v[3]) v[2] = v[3];
                 for (int q = 0; q < 4; ++q) p.diag_out[q] = v[q];
                 p.diag->ticket = 0;
             }
@@ -317,9 +477,9 @@ static int env_int_(const char* name, int dflt) {
     return e ? atoi(e) : dflt;
 }
 
-template <int SRB, int RPT>
-static int launch_t2(const CUtensorMap& mT, const CUtensorMap& mC, const T2Params& p, cudaStream_t st) {
-    auto kern = diff2d_temporal2_kernel<SRB, RPT>;
+template <int SRB, int RPT, bool DIAG>
+static int launch_t2d(const CUtensorMap& mT, const CUtensorMap& mC, const T2Params& p, cudaStream_t st) {
+    auto kern = diff2d_temporal2_kernel<SRB, RPT, DIAG>;
     constexpr int T2_SMEM_BYTES = t2_smem_bytes(SRB);
     static bool attr_set[64] = {false};
     int dev = 0;
@@ -328,7 +488,7 @@ static int launch_t2(const CUtensorMap& mT, const CUtensorMap& mC, const T2Param
         IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    const int slots = igg::sm_count() * (SRB == 8 ? 2 : 1);      // 8-row blocks: two CTAs per SM
+    const int slots = igg::sm_count() * (SRB == 4 ? 4 : (SRB == 8 ? 2 : 1));   // small blocks: several CTAs per SM
     const int nitems = num_items(p.g);
     const int grid = nitems < slots ? nitems : slots;
     if (grid > 1024) {
@@ -339,13 +499,18 @@ static int launch_t2(const CUtensorMap& mT, const CUtensorMap& mC, const T2Param
     return 0;
 }
 
+template <int SRB, int RPT>
+static int launch_t2(const CUtensorMap& mT, const CUtensorMap& mC, const T2Params& p, cudaStream_t st) {
+    return p.diag_out ? launch_t2d<SRB, RPT, true>(mT, mC, p, st) : launch_t2d<SRB, RPT, false>(mT, mC, p, st);
+}
+
 }  // namespace
 
 extern "C" int igg_temporal2d_default_rows(void) {
     static int v = -1;
     if (v < 0) {
         v = env_int_("IGG_T2_ROWS", 252);
-        if (v < 12 || (v + 4) % 16) v = 252;        // (rows + 4) must be a multiple of the block height (8 or 16)
+        if (v < 12 || (v + 4) % 16) v = 252;        // (rows + 4) must be a multiple of the block height (4, 8 or 16)
     }
     return v;
 }
@@ -366,11 +531,17 @@ extern "C" int igg_diffusion2d_step2(const double* T, double* T2, const double* 
     T2Params p;
     memset(&p, 0, sizeof(p));
     p.T2 = T2;
-    static int srb = -1, rpt = -1;
+    static int srb = -1, rpt = -1, lean = 1;
     if (srb < 0) {
-        srb = env_int_("IGG_T2_SRB", 8) == 16 ? 16 : 8;      // 8: two CTAs per SM (0.675 vs 0.709 ms per step at 16384^2)
+        // rows per block: 4 -> four CTAs of 160 threads per SM (0.539 ms per step at 16384^2), 8 -> two of 288
+        // (0.570), 16 -> one of 544 (0.612); measured in one call, profiles/r2/t2_lean_sweep.txt
+        const int e = env_int_("IGG_T2_SRB", 4);
         rpt = env_int_("IGG_T2_RPT", 2) == 4 ? 4 : 2;
+        lean = env_int_("IGG_T2_LEAN", 1);
+        srb = e == 16 ? 16 : (e == 8 ? 8 : 4);
+        if (srb == 4) rpt = 2;
     }
+    p.lean = lean;
     p.g = make_geom(nx, ny, srb, igg_temporal2d_default_rows(), push ? 1 : 0);
     p.ph.lam = lam; p.ph.dt = dt; p.ph._dx = _dx; p.ph._dy = _dy;
     p.dev_params = opts ? opts->dev_params : nullptr;
@@ -415,6 +586,7 @@ extern "C" int igg_diffusion2d_step2(const double* T, double* T2, const double* 
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     if (srb == 16 && rpt == 4) rc = launch_t2<16, 4>(mT, mC, p, st);
+    else if (srb == 4) rc = launch_t2<4, 2>(mT, mC, p, st);
     else if (srb == 16) rc = launch_t2<16, 2>(mT, mC, p, st);
     else if (rpt == 4) rc = launch_t2<8, 4>(mT, mC, p, st);
     else rc = launch_t2<8, 2>(mT, mC, p, st);

@@ -116,8 +116,9 @@ extern "C" int igg_cpu_temporal2d_emulate(const double* T, double* T2, const dou
                                           int workers, const double* mid_lines, int side_mask,
                                           const double* phys2, double* diag_out) {
     if (!T || !T2 || !Cp || nx < 3 || ny < 4 || (ny & 1)) return IGG_ERR_INVALID;
-    if (srb != 8 && srb != 16) return IGG_ERR_INVALID;
-    if (scx < srb - 4 || (scx + 4) % srb || workers < 1 || (rpt != 2 && rpt != 4)) return IGG_ERR_INVALID;
+    if (srb != 4 && srb != 8 && srb != 16) return IGG_ERR_INVALID;
+    if (scx < srb - 4 || scx < 4 || (scx + 4) % srb || workers < 1 || (rpt != 2 && rpt != 4)) return IGG_ERR_INVALID;
+    if (srb == 4 && rpt != 2) return IGG_ERR_INVALID;
     if (side_mask && !mid_lines) return IGG_ERR_INVALID;
     const Geom g = make_geom(nx, ny, srb, scx, side_mask ? 1 : 0);
     Phys ph;
@@ -137,7 +138,8 @@ extern "C" int igg_cpu_temporal2d_emulate(const double* T, double* T2, const dou
         ph2._dx = phys2[2];
         ph2._dy = phys2[3];
     }
-    if (srb == 16 && rpt == 4) emulate<16, 4>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
+    if (srb == 4) emulate<4, 2>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
+    else if (srb == 16 && rpt == 4) emulate<16, 4>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
     else if (srb == 16) emulate<16, 2>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
     else if (rpt == 4) emulate<8, 4>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
     else emulate<8, 2>(T, T2, Cp, g, ph, ph2, workers, ml, diag_out);
