@@ -328,12 +328,9 @@ def main() -> int:
         nvl = 770.0                                   # measured peer copy, GB/s per direction per GPU (profiling recipe)
         # bytes this rank sends per step: one edge line per existing face neighbour (+ 8 B per corner); the
         # two-step mode sends a mid line and an edge line per PAIR of steps -- the same per step
-        faces = [(0, -1), (0, 1), (1, -1), (1, 1)]
-        n_face = {0: 0, 1: 0}
-        for d, sgn in faces:
-            if dims[d] > 1:
-                n_face[d] += 1 if dims[d] == 2 else 2      # interior ranks have both neighbours (worst rank counts)
-        halo_bytes = 8 * (min(n_face[0], 2) * ny + min(n_face[1], 2) * nx)
+        # face neighbours of the busiest rank per dimension: none (dims 1), one (dims 2), two (dims > 2)
+        n_face = [0 if dims[d] == 1 else (1 if dims[d] == 2 else 2) for d in range(2)]
+        halo_bytes = 8 * (n_face[0] * ny + n_face[1] * nx)
         hbm_term = A_eff / steps_per_pass / hbm * 1e3 if steps_per_pass > 1 else A_eff / hbm * 1e3
         dram_bytes_step = A_eff / steps_per_pass if steps_per_pass > 1 else A_eff
         nvl_term = halo_bytes / 1e9 / nvl * 1e3

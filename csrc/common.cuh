@@ -194,6 +194,22 @@ __device__ __forceinline__ bool wait_flag_ge_relaxed(const uint64_t* p, uint64_t
 // the reference's maximum(T_v) (scripts/diffusion_2D_perf_hide.jl:115)
 __device__ __forceinline__ double max_nan(double a, double b) { return (a > b || a != a) ? a : b; }
 
+// One cell of the reference's THREE-kernel form fused into one expression with its roundings kept
+// (scripts/diffusion_2D_kp.jl: Flux! :20,:23 -> Residual! :37 -> Update! :51): the fluxes are rounded products
+// (they are stored to qx / qy there, so no multiply may be contracted into the following subtraction),
+// dTdt = 1.0/Cp * -((qxR - qxL)*_dx + (qyT - qyB)*_dy) -- a DIVISION by Cp where the perf form multiplies --
+// and T + dt*dTdt.  Used by the single-launch multi-step kernels when they serve the kp application.
+__device__ __forceinline__ double update_cell_kp(double c, double xm, double xp, double ym, double yp, double cp,
+                                                 double lam, double dt, double _dx, double _dy) {
+    const double qxr = __dmul_rn(__dmul_rn(-lam, xp - c), _dx);
+    const double qxl = __dmul_rn(__dmul_rn(-lam, c - xm), _dx);
+    const double qyt = __dmul_rn(__dmul_rn(-lam, yp - c), _dy);
+    const double qyb = __dmul_rn(__dmul_rn(-lam, c - ym), _dy);
+    const double dqx = qxr - qxl, dqy = qyt - qyb;
+    const double dTdt = 1.0 / cp * -(dqx * _dx + dqy * _dy);
+    return c + dt * dTdt;
+}
+
 // streaming (evict-first) 16-byte / 8-byte global stores and read-only loads
 __device__ __forceinline__ void st_cs_f64x2(double* p, double a, double b) {
     asm volatile("st.global.cs.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");

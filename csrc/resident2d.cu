@@ -46,6 +46,7 @@ struct ResParams {
     uint64_t* peer_land[9];     // base of the neighbour's landing buffer (NULL = flag mode or no neighbour)
     uint64_t* my_land;          // mine: [parity][source offset][index along the edge][2 words]
     int land_len;               // entries per (parity, offset) region
+    int form;                   // 0 = perf form, 1 = kp form (update_cell_kp)
 };
 
 // landing-buffer helpers ---------------------------------------------------------------------------------
@@ -134,8 +135,10 @@ __global__ void __launch_bounds__(RES_THREADS, 1) diff2d_resident_kernel(const _
                 const double cc = row[y];
                 const double xm = lr > 0 ? row[y - ny] : up_src[y];
                 const double xp = lr + 1 < nr ? row[y + ny] : dn_src[y];
-                const double v = upd(cc, xm, xp, row[y - 1], row[y + 1], bufC[(size_t)lr * ny + y], p.lam, p.dt,
-                                     p._dx, p._dy);
+                const double v = p.form ? update_cell_kp(cc, xm, xp, row[y - 1], row[y + 1], bufC[(size_t)lr * ny + y],
+                                                         p.lam, p.dt, p._dx, p._dy)
+                                        : upd(cc, xm, xp, row[y - 1], row[y + 1], bufC[(size_t)lr * ny + y], p.lam, p.dt,
+                                              p._dx, p._dy);
                 dst[(size_t)lr * ny + y] = v;
                 // edge cells go to the neighbouring GPUs' halo cells
                 const bool xl = x == 1, xh = x == nx - 2, yl = y == 1, yh = y == ny - 2;
@@ -268,7 +271,18 @@ extern "C" int igg_diffusion2d_resident(double* T, double* T2, const double* Cp,
                                         double* const* peer_T2, uint64_t* const* peer_flags, uint64_t* my_flags,
                                         uint64_t epoch0, uint64_t* const* peer_land, uint64_t* my_land, int land_len,
                                         int* cluster_size_out, void* stream) {
+    return igg_diffusion2d_resident_ex(T, T2, Cp, nx, ny, lam, dt, _dx, _dy, nsteps, 0, peer_T, peer_T2, peer_flags,
+                                       my_flags, epoch0, peer_land, my_land, land_len, cluster_size_out, stream);
+}
+
+extern "C" int igg_diffusion2d_resident_ex(double* T, double* T2, const double* Cp, int nx, int ny, double lam,
+                                           double dt, double _dx, double _dy, int nsteps, int form,
+                                           double* const* peer_T, double* const* peer_T2,
+                                           uint64_t* const* peer_flags, uint64_t* my_flags, uint64_t epoch0,
+                                           uint64_t* const* peer_land, uint64_t* my_land, int land_len,
+                                           int* cluster_size_out, void* stream) {
     IGG_REQUIRE(T && T2 && Cp && nx >= 3 && ny >= 3 && nsteps >= 1, "igg_diffusion2d_resident: bad arguments");
+    IGG_REQUIRE(form == 0 || form == 1, "igg_diffusion2d_resident: form must be 0 (perf) or 1 (kp)");
     const bool comm = peer_flags != nullptr || peer_land != nullptr;
     IGG_REQUIRE(!comm || (my_flags && epoch0 >= 1), "igg_diffusion2d_resident: communication needs my_flags and epoch0 >= 1");
     IGG_REQUIRE(!peer_flags || (peer_T && peer_T2), "igg_diffusion2d_resident: flag mode needs the peer array tables");
@@ -297,6 +311,7 @@ extern "C" int igg_diffusion2d_resident(double* T, double* T2, const double* Cp,
     memset(&p, 0, sizeof(p));
     p.T = T; p.T2 = T2; p.Cp = Cp; p.nx = nx; p.ny = ny; p.R = R; p.nsteps = nsteps;
     p.lam = lam; p.dt = dt; p._dx = _dx; p._dy = _dy;
+    p.form = form;
     if (comm) {
         for (int o = 0; o < 9; ++o) {
             if (peer_flags && !peer_land) {

@@ -776,6 +776,7 @@ struct MSParams {
     Params p;                   // step 0 reads p.T and writes p.T2; push.peer_dst = neighbours' T2
     double* peer_dst_odd[9];    // odd steps write T: neighbours' T
     int nsteps;
+    int form;                   // 0 = fused perf form (perf.jl:8-10), 1 = kp form (kp.jl:20-51, divides by Cp)
     unsigned long long* gbar;   // grid-barrier counter (monotonic)
     unsigned long long gbar_base;
 };
@@ -826,8 +827,10 @@ __global__ void __launch_bounds__(256) diff2d_multistep_kernel(const __grid_cons
                 for (int r = 0; r < MROWS; ++r) {
                     const int x = xb + r;
                     if (x >= 1 && x <= nx - 2) {
-                        const double v = update_cell(col[r + 1], col[r], col[r + 2], lf[r], rt[r], cpv[r], p.lam, p.dt,
-                                                     p._dx, p._dy);
+                        const double v = q.form ? update_cell_kp(col[r + 1], col[r], col[r + 2], lf[r], rt[r], cpv[r],
+                                                                 p.lam, p.dt, p._dx, p._dy)
+                                                : update_cell(col[r + 1], col[r], col[r + 2], lf[r], rt[r], cpv[r], p.lam,
+                                                              p.dt, p._dx, p._dy);
                         dst[(size_t)x * ny + y] = v;
                         if (edge_tile) push_cell_2d_to(peers, nx, ny, x, y, v);
                     }
@@ -858,7 +861,17 @@ extern "C" int igg_diffusion2d_multistep(double* T, double* T2, const double* Cp
                                          double _dx, double _dy, int nsteps, const igg_push2d* push_even,
                                          double* const* peer_dst_odd, unsigned long long* grid_barrier,
                                          unsigned long long grid_barrier_base, int* grid_size_out, void* stream) {
+    return igg_diffusion2d_multistep_ex(T, T2, Cp, nx, ny, lam, dt, _dx, _dy, nsteps, 0, push_even, peer_dst_odd,
+                                        grid_barrier, grid_barrier_base, grid_size_out, stream);
+}
+
+extern "C" int igg_diffusion2d_multistep_ex(double* T, double* T2, const double* Cp, int nx, int ny, double lam,
+                                            double dt, double _dx, double _dy, int nsteps, int form,
+                                            const igg_push2d* push_even, double* const* peer_dst_odd,
+                                            unsigned long long* grid_barrier, unsigned long long grid_barrier_base,
+                                            int* grid_size_out, void* stream) {
     IGG_REQUIRE(T && T2 && Cp && grid_barrier, "igg_diffusion2d_multistep: null pointer");
+    IGG_REQUIRE(form == 0 || form == 1, "igg_diffusion2d_multistep: form must be 0 (perf) or 1 (kp)");
     IGG_REQUIRE(nx >= 3 && ny >= 3 && nsteps >= 1, "igg_diffusion2d_multistep: bad sizes");
     IGG_REQUIRE(!push_even || peer_dst_odd, "igg_diffusion2d_multistep: a push needs both destination tables");
     MSParams q;
@@ -890,6 +903,7 @@ extern "C" int igg_diffusion2d_multistep(double* T, double* T2, const double* Cp
         }
     }
     q.nsteps = nsteps;
+    q.form = form;
     q.gbar = grid_barrier;
     q.gbar_base = grid_barrier_base;
     // all CTAs must be co-resident (they wait for one another): cooperative launch, grid <= what fits

@@ -148,9 +148,8 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
                 if (DIAG) {
                     const int xr = x + 1 + r;          // global row of this mid value
                     if (pair_ok && xr >= x_lo && xr <= x_hi) {
-                        acc.d1max = fmax(fmax(acc.d1max, mA), mB);
-                        acc.d1sum += mA;
-                        acc.d1sum += mB;
+                        acc.d1max = fmax(acc.d1max, fmax(mA, mB));      // one dependent op per row on each accumulator
+                        acc.d1sum += mA + mB;
                     }
                 }
                 a = bb;
@@ -181,9 +180,8 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
                 if (pair_ok && xr >= x_lo && xr <= x_hi) {
                     st_cs_f64x2(out + (size_t)r * ny, oA, oB);
                     if (DIAG) {
-                        acc.d2max = fmax(fmax(acc.d2max, oA), oB);
-                        acc.d2sum += oA;
-                        acc.d2sum += oB;
+                        acc.d2max = fmax(acc.d2max, fmax(oA, oB));
+                        acc.d2sum += oA + oB;
                     }
                 }
                 a = bb;

@@ -119,6 +119,13 @@ int igg_diffusion2d_multistep(double* T, double* T2, const double* Cp, int nx, i
                               double _dx, double _dy, int nsteps, const igg_push2d* push_even,
                               double* const* peer_dst_odd, unsigned long long* grid_barrier,
                               unsigned long long grid_barrier_base, int* grid_size_out, void* stream);
+/* The same with the step arithmetic selectable: form 0 = fused perf form (scripts/diffusion_2D_perf.jl:8-10), form 1 =
+ * the kp application's three kernels folded into one expression with their roundings kept (Flux! / Residual! /
+ * Update!, scripts/diffusion_2D_kp.jl:20-51: rounded flux products, DIVISION by Cp) -- the fast path of the kp app. */
+int igg_diffusion2d_multistep_ex(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
+                                 double _dx, double _dy, int nsteps, int form, const igg_push2d* push_even,
+                                 double* const* peer_dst_odd, unsigned long long* grid_barrier,
+                                 unsigned long long grid_barrier_base, int* grid_size_out, void* stream);
 
 /* `nsteps` steps with the whole local field resident in the shared memory of ONE thread-block cluster
  * (<= 16 CTAs): rows shared between CTAs are read through distributed shared memory, steps are separated by
@@ -140,6 +147,12 @@ int igg_diffusion2d_resident(double* T, double* T2, const double* Cp, int nx, in
                              uint64_t* const* peer_flags, uint64_t* my_flags, uint64_t epoch0,
                              uint64_t* const* peer_land, uint64_t* my_land, int land_len,
                              int* cluster_size_out, void* stream);
+/* form as in igg_diffusion2d_multistep_ex (1 = kp arithmetic) */
+int igg_diffusion2d_resident_ex(double* T, double* T2, const double* Cp, int nx, int ny, double lam, double dt,
+                                double _dx, double _dy, int nsteps, int form, double* const* peer_T,
+                                double* const* peer_T2, uint64_t* const* peer_flags, uint64_t* my_flags,
+                                uint64_t epoch0, uint64_t* const* peer_land, uint64_t* my_land, int land_len,
+                                int* cluster_size_out, void* stream);
 
 /* ---- 2-D diffusion, two steps per pass over memory (no reference counterpart: its loop,
  *      scripts/diffusion_2D_perf.jl:47-52, makes one trip through memory per step) -----------------

@@ -13,6 +13,13 @@ Halo handling (``--transport``):
   before ``Update!`` overwrites what the neighbours' ``Flux!`` is still reading.
 * ``nccl`` / ``host``: the three kernels, then ``update_halo(T)`` with pack -> send/recv -> unpack.
 
+Fast path (``--kp-path auto|resident|persistent``, CUDA only): the reference runs kp at sizes where a step is pure
+launch latency (128 x 128, ``scripts/diffusion_2D_kp.jl:61``; three launches, three host waits and an exchange per
+step, ``:88-91``).  The single-launch kernels behind ``Diffusion2D(mode='resident' | 'persistent')`` therefore
+also come with the kp arithmetic (``form='kp'``: rounded flux products, division by ``Cp``, ``T + dt*dTdt``): all
+``nt`` steps are ONE launch, halo cells travel as in-kernel peer stores, and ``qx``, ``qy``, ``dTdt`` never exist in
+memory.  ``three`` (default) keeps the literal three kernels.
+
 Run:  ``torchrun --nproc-per-node 8 -m rocm_mpi_b200.models.diffusion2d_kp --nx 65 --ny 128 --dimx 4 --dimy 2``
 """
 from __future__ import annotations
@@ -45,6 +52,10 @@ def diffusion2D_kp(cfg: DiffusionConfig = None, finalize: bool = True) -> RunRes
     _dx, _dy = 1.0 / s.dx, 1.0 / s.dy
     transport = cfg.transport or default_transport(torch.empty(0, device=dev))
     comm_needed = g.nprocs > 1 or any(g.periods)
+    if cfg.kp_path not in ("three", "persistent", "resident", "auto"):
+        raise ValueError("kp_path must be three | persistent | resident | auto")
+    if on_gpu and cfg.kp_path != "three":
+        return _single_launch(cfg, s, finalize)
     fused_push = on_gpu and transport == "peer" and cfg.fused and comm_needed
     # Array initializations (reference scripts/diffusion_2D_kp.jl:73-78)
     dTdt = torch.zeros(nx - 2, ny - 2, dtype=f64, device=dev)
@@ -97,6 +108,35 @@ def diffusion2D_kp(cfg: DiffusionConfig = None, finalize: bool = True) -> RunRes
     if plan is not None:
         plan.finish()
     log0("done")
+    res = RunResult("kp", s.me, s.nprocs, s.dims, int(cfg.nt), T_local=T, launches=native.launch_count() - n0)
+    if cfg.do_vis:
+        visualise_2d(s, T, "kp", res)
+    if finalize:
+        detach_local(res)
+        finalize_global_grid()
+    return res
+
+
+def _single_launch(cfg: DiffusionConfig, s, finalize: bool) -> RunResult:
+    """All ``nt`` steps of the kp arithmetic in one launch (``Diffusion2D(form='kp')``)."""
+    from .solver import Diffusion2D
+    n0 = native.launch_count()
+    modes = {"resident": ["resident"], "persistent": ["persistent"], "auto": ["resident", "persistent"]}[cfg.kp_path]
+    sol = None
+    log0("Starting the time loop ...", end="")
+    for k, mode in enumerate(modes):
+        sol = Diffusion2D(cfg.nx, cfg.ny, lx=cfg.lx, ly=cfg.ly, lam=cfg.lam, Cp0=cfg.Cp0, mode=mode, form="kp")
+        try:
+            sol.begin()
+            sol.step(int(cfg.nt))
+            sol.finish()
+            break
+        except native.NativeError as e:       # field too large for one cluster: every rank takes the same branch
+            if k + 1 == len(modes) or "does not fit" not in str(e):
+                raise
+            sol.close()
+    log0("done")
+    T = sol.T
     res = RunResult("kp", s.me, s.nprocs, s.dims, int(cfg.nt), T_local=T, launches=native.launch_count() - n0)
     if cfg.do_vis:
         visualise_2d(s, T, "kp", res)

@@ -49,7 +49,7 @@ __all__ = ["Diffusion2D"]
 class Diffusion2D:
     def __init__(self, nx: int, ny: int, *, lx: float = 10.0, ly: float = 10.0, lam: float = 1.0, Cp0: float = 1.0,
                  mode: str = "fused", variant: str = "tma", b_width: Sequence[int] = (16, 4),
-                 transport: Optional[str] = None, host_ic: bool = False) -> None:
+                 transport: Optional[str] = None, host_ic: bool = False, form: str = "perf") -> None:
         g = global_grid()
         if g.device_type != "cuda":
             raise RuntimeError("Diffusion2D runs on CUDA devices; use models.diffusion2d_ap on CPU")
@@ -57,6 +57,11 @@ class Diffusion2D:
             raise ValueError("nx, ny must be the local sizes given to init_global_grid")
         if mode not in ("fused", "hide", "hide_exchange", "plain", "persistent", "resident", "temporal"):
             raise ValueError("mode must be fused | hide | hide_exchange | plain | persistent | resident | temporal")
+        if form not in ("perf", "kp"):
+            raise ValueError("form must be 'perf' or 'kp'")
+        if form == "kp" and mode not in ("persistent", "resident"):
+            raise ValueError("form='kp' (the kp application's arithmetic) exists for mode='persistent' and 'resident'")
+        self.form = form
         if mode == "temporal" and variant != "tma":
             raise ValueError("mode='temporal' is a TMA kernel (variant='tma', even ny)")
         native.require()
@@ -220,7 +225,7 @@ class Diffusion2D:
             native.diffusion2d_resident(self.T, self.T2, self.Cp, self.lam, self.dt, self._dx, self._dy, n, pT, pT2,
                                         pF, self._rflags.data_ptr(), self._repoch + 1, pL,
                                         self._rland.data_ptr() if (self._rll and pL is not None) else 0,
-                                        self._rland_len)
+                                        self._rland_len, form=self.form)
             self._repoch += n
             if n % 2:
                 self.T, self.T2 = self.T2, self.T
@@ -254,7 +259,7 @@ class Diffusion2D:
                 pe, po = self.plan._desc[self.T2.data_ptr()], self.plan._desc[self.T.data_ptr()]
                 pe.epoch = self.plan.epoch + 1
             grid = native.diffusion2d_multistep(self.T, self.T2, self.Cp, self.lam, self.dt, self._dx, self._dy, n,
-                                                self._gbar, self._gbar_base, pe, po)
+                                                self._gbar, self._gbar_base, pe, po, form=self.form)
             self._gbar_base += n * grid
             self.plan.epoch += n if self.plan.fab.neighbors else 0
             if n % 2:

@@ -81,6 +81,10 @@ def _declare(lib) -> None:
         "igg_event_wait": ([vp, i], i),
         "igg_diffusion2d_resident": ([vp, vp, vp, i, i, d, d, d, d, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), vp,
                                      u64, C.POINTER(vp), vp, i, C.POINTER(i), vp], i),
+        "igg_diffusion2d_resident_ex": ([vp, vp, vp, i, i, d, d, d, d, i, i, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
+                                        vp, u64, C.POINTER(vp), vp, i, C.POINTER(i), vp], i),
+        "igg_diffusion2d_multistep_ex": ([vp, vp, vp, i, i, d, d, d, d, i, i, C.POINTER(Push2D), C.POINTER(vp), vp,
+                                         C.c_ulonglong, C.POINTER(i), vp], i),
         "igg_diffusion2d_run": ([vp, vp, vp, i, i, d, d, d, d, i, i, i, i, C.POINTER(Push2D), C.POINTER(Push2D), vp], i),
         "igg_diffusion2d_multistep": ([vp, vp, vp, i, i, d, d, d, d, i, C.POINTER(Push2D), C.POINTER(vp), vp,
                                       C.c_ulonglong, C.POINTER(i), vp], i),
@@ -197,6 +201,7 @@ def device_info() -> dict:
 
 # ---- stencils ---------------------------------------------------------------------------------------
 VARIANTS = {"direct": 0, "tma": 1}
+FORMS = {"perf": 0, "kp": 1}       # step arithmetic of the single-launch multi-step kernels
 
 
 def diffusion2d_step(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
@@ -372,7 +377,7 @@ def diffusion2d_step_controlled(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Ten
 
 def diffusion2d_resident(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
                          _dy: float, nsteps: int, peer_T=None, peer_T2=None, peer_flags=None, my_flags: int = 0,
-                         epoch0: int = 0, peer_land=None, my_land: int = 0, land_len: int = 0) -> int:
+                         epoch0: int = 0, peer_land=None, my_land: int = 0, land_len: int = 0, form: str = "perf") -> int:
     """``nsteps`` steps with the field resident in one thread-block cluster (``igg_diffusion2d_resident``).
 
     ``peer_T`` / ``peer_T2`` / ``peer_flags``: sequences of 9 raw pointers (0 = no neighbour) indexed
@@ -389,9 +394,9 @@ def diffusion2d_resident(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, la
         f = (C.c_void_p * 9)(*[x or None for x in peer_flags])
     if peer_land is not None:
         ld = (C.c_void_p * 9)(*[x or None for x in peer_land])
-    _check(lib.igg_diffusion2d_resident(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
-                                        int(nsteps), a, b, f, my_flags or None, int(epoch0), ld, my_land or None,
-                                        int(land_len), C.byref(csz), _stream()))
+    _check(lib.igg_diffusion2d_resident_ex(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
+                                           int(nsteps), FORMS[form], a, b, f, my_flags or None, int(epoch0), ld,
+                                           my_land or None, int(land_len), C.byref(csz), _stream()))
     return csz.value
 
 
@@ -410,8 +415,10 @@ def diffusion2d_run(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam: fl
 
 def diffusion2d_multistep(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, lam: float, dt: float, _dx: float,
                           _dy: float, nsteps: int, grid_barrier: torch.Tensor, barrier_base: int,
-                          push_even: Optional[Push2D] = None, push_odd: Optional[Push2D] = None) -> int:
-    """``nsteps`` fused steps in one cooperative launch (``igg_diffusion2d_multistep``).
+                          push_even: Optional[Push2D] = None, push_odd: Optional[Push2D] = None,
+                          form: str = "perf") -> int:
+    """``nsteps`` fused steps in one cooperative launch (``igg_diffusion2d_multistep_ex``); ``form='kp'`` selects the
+    arithmetic of the kp application (``Flux!`` / ``Residual!`` / ``Update!`` with their roundings, division by Cp).
 
     Returns the grid size used (the barrier counter advances by ``nsteps * grid``).  ``push_even`` /
     ``push_odd`` are the plan descriptors whose destinations are the neighbours' ``T2`` / ``T``."""
@@ -421,9 +428,10 @@ def diffusion2d_multistep(T: torch.Tensor, T2: torch.Tensor, Cp: torch.Tensor, l
     odd = None
     if push_even is not None:
         odd = (C.c_void_p * 9)(*[push_odd.peer_dst[k] for k in range(9)])
-    _check(lib.igg_diffusion2d_multistep(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
-                                         int(nsteps), C.byref(push_even) if push_even is not None else None, odd,
-                                         grid_barrier.data_ptr(), int(barrier_base), C.byref(grid), _stream()))
+    _check(lib.igg_diffusion2d_multistep_ex(_f64(T, "T"), _f64(T2, "T2"), _f64(Cp, "Cp"), nx, ny, lam, dt, _dx, _dy,
+                                            int(nsteps), FORMS[form],
+                                            C.byref(push_even) if push_even is not None else None, odd,
+                                            grid_barrier.data_ptr(), int(barrier_base), C.byref(grid), _stream()))
     return grid.value
 
 

@@ -318,6 +318,7 @@ class PeerHalo:
         self.bank = self.fab.new_bank()
         self.epoch = 0
         self._tables: Dict[tuple, Tuple[torch.Tensor, int, int]] = {}
+        self._sync = None
         self.launches = 0
 
     def _boxes(self, A: torch.Tensor):
@@ -379,8 +380,11 @@ class PeerHalo:
         if not self.fab.neighbors:
             return
         self.epoch += 1
-        sync = self.fab.sync_struct(self.bank, self.epoch)
-        native._check(self.fab.lib.igg_halo_exchange_peer_ex(dev.data_ptr(), n, C.byref(sync), ctas,
+        if self._sync is None:              # the neighbour banks never change: build the struct once
+            self._sync = self.fab.sync_struct(self.bank, self.epoch)
+            self._sync_ref = C.byref(self._sync)
+        self._sync.epoch = self.epoch
+        native._check(self.fab.lib.igg_halo_exchange_peer_ex(dev.data_ptr(), n, self._sync_ref, ctas,
                                                              native._stream()))
         self.launches += 1
         if self.launches % self.CHECK_EVERY == 0:

@@ -50,6 +50,9 @@ class DiffusionConfig:
     transport: Optional[str] = None              # peer | nccl | host | gloo (None = default)
     kernel: str = "tma"                          # tma | direct  (stencil kernel flavour)
     fused: bool = True                           # fuse the halo push into the stencil kernel
+    kp_path: str = "three"                       # kp app on CUDA: three (Flux!/Residual!/Update! launches per step,
+                                                 # the literal form) | persistent | resident | auto (ONE launch for
+                                                 # all nt steps with the kp arithmetic; auto = resident if it fits)
     device_type: str = "auto"
     # checkpoint / resume (none in the reference)
     ckpt_every: int = 0                          # write a checkpoint every N steps (0 = never)

@@ -43,6 +43,45 @@ def test_kp_app_periodic_fused_push(tmp_path):
     assert float((T - Th).abs().max()) < 1e-12
 
 
+@pytest.mark.parametrize("path", ["resident", "persistent"])
+def test_kp_app_single_launch_paths_match_oracle_and_three_kernels(tmp_path, path):
+    """``kp_path``: all nt steps in one launch with the kp arithmetic (reference scripts/diffusion_2D_kp.jl:20-51)."""
+    from rocm_mpi_b200.models.diffusion2d_kp import diffusion2D_kp
+    T_ref, _ = ref.oracle_2d(128, 128, 100, "kp")
+    three = diffusion2D_kp(DiffusionConfig(nx=128, ny=128, nt=100, outdir=str(tmp_path), quiet=True))
+    res = diffusion2D_kp(DiffusionConfig(nx=128, ny=128, nt=100, outdir=str(tmp_path), quiet=True, kp_path=path))
+    assert float((res.T_v - T_ref[1:-1, 1:-1]).abs().max()) < 1e-12
+    assert float((res.T_v - three.T_v).abs().max()) < 1e-13
+    assert res.launches <= 3          # IC + ONE stepping launch (+ interior extraction), not 300
+
+
+@pytest.mark.parametrize("mode", ["resident", "persistent"])
+def test_kp_form_divides_by_cp(mode):
+    """A non-constant Cp separates the kp form (1/Cp) from the perf form (Cp *); periodic = self-neighbour pushes."""
+    from rocm_mpi_b200.models.solver import Diffusion2D
+    nx, ny, nt = 66, 128, 12
+    igg.init_global_grid(nx, ny, 1, periodx=1, periody=1, quiet=True, init_dist=False)
+    s = Diffusion2D(nx, ny, mode=mode, form="kp")
+    g = torch.Generator().manual_seed(5)
+    Cp = torch.rand(nx, ny, generator=g, dtype=torch.float64) + 0.5
+    s.Cp.copy_(Cp)
+    Th = s.T.cpu().clone()
+    s.begin()
+    s.step(nt)
+    s.finish()
+    got = s.T.cpu()
+    dx, dy, dt = s.dx, s.dy, s.dt
+    igg.finalize_global_grid(finalize_dist=False)
+    vg = igg.VirtualGrid((nx, ny), (1, 1), (1, 1))
+    qx, qy, dd = torch.zeros(nx - 1, ny - 2, dtype=torch.float64), torch.zeros(nx - 2, ny - 1, dtype=torch.float64), \
+        torch.zeros(nx - 2, ny - 2, dtype=torch.float64)
+    vg.update_halo([Th])
+    for _ in range(nt):
+        ref.kp_step(Th, Cp, qx, qy, dd, 1.0, dt, 1.0 / dx, 1.0 / dy)
+        vg.update_halo([Th])
+    assert float((got - Th).abs().max()) < 1e-12
+
+
 def test_perf_and_hide_apps_small(tmp_path):
     from rocm_mpi_b200.models.diffusion2d_perf import diffusion2D_perf
     from rocm_mpi_b200.models.diffusion2d_perf_hide import diffusion2D_perf_hide
