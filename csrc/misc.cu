@@ -53,13 +53,77 @@ __global__ void unpack_plane_kernel(double* __restrict__ A, int n0, int n1, int 
         A[plane_elem(n0, n1, n2, dim, idx, e)] = buf[e];
 }
 
-__global__ void extract_inner_kernel(const double* __restrict__ A, int n0, int n1, int n2, int m0, int m1, int m2,
-                                     int o0, int o1, int o2, double* __restrict__ out) {
-    const size_t count = (size_t)m0 * m1 * m2;
-    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < count; e += (size_t)gridDim.x * blockDim.x) {
-        const size_t c = e % m2, b = (e / m2) % m1, a = e / ((size_t)m1 * m2);
-        out[e] = A[((a + o0) * n1 + (b + o1)) * n2 + (c + o2)];
+// Halo-free interior of A (n0 x n1 x n2, last index contiguous) copied row by row into a block of a larger array G
+// (row pitches G1*G2 and G2, block origin g0, g1, g2): the dense buffer of extract_inner when G is the interior
+// itself, or -- with G peer-mapped -- this rank's tile of the gathered field in the ROOT's memory (gather without
+// host staging).  A CTA takes whole rows (one division per row, none per element); a thread moves two doubles per
+// unit: two 8-byte loads (the interior starts one element into the row, so the source is only 8-byte aligned) and one
+// 16-byte store when the destination is 16-byte aligned -- the width NVLink stores want -- else two 8-byte stores.
+constexpr int CIR_THREADS = 256;
+__global__ void __launch_bounds__(CIR_THREADS) copy_inner_rows_kernel(const double* __restrict__ A, int n1, int n2,
+                                                                      int m1, int m2, int o0, int o1, int o2,
+                                                                      double* __restrict__ G, long long G1, long long G2,
+                                                                      long long g0, long long g1, long long g2,
+                                                                      long long rows) {
+    const int upr = m2 >> 1;                          // two-element units per row (+ one tail element if m2 is odd)
+    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+        const long long a = row / m1, b = row - a * m1;
+        const double* __restrict__ src = A + ((a + o0) * (long long)n1 + (b + o1)) * (long long)n2 + o2;
+        double* __restrict__ dst = G + ((a + g0) * G1 + (b + g1)) * G2 + g2;
+        const bool al16 = (((uintptr_t)dst) & 15) == 0;
+        int u = threadIdx.x;
+        for (; u + 3 * CIR_THREADS < upr; u += 4 * CIR_THREADS) {      // four units in flight per thread
+            double x[4], y[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                x[q] = src[2 * (u + q * CIR_THREADS)];
+                y[q] = src[2 * (u + q * CIR_THREADS) + 1];
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                double* d = dst + 2 * (u + q * CIR_THREADS);
+                if (al16) {
+                    *reinterpret_cast<double2*>(d) = make_double2(x[q], y[q]);
+                } else {
+                    d[0] = x[q];
+                    d[1] = y[q];
+                }
+            }
+        }
+        for (; u < upr; u += CIR_THREADS) {
+            const double x = src[2 * u], y = src[2 * u + 1];
+            if (al16) {
+                *reinterpret_cast<double2*>(dst + 2 * u) = make_double2(x, y);
+            } else {
+                dst[2 * u] = x;
+                dst[2 * u + 1] = y;
+            }
+        }
+        if ((m2 & 1) && threadIdx.x == 0) dst[m2 - 1] = src[m2 - 1];
     }
+}
+
+// shape with trailing singleton dimensions moved to the front, so that the LAST entry is the contiguous one
+static void canonical_shape(int& n0, int& n1, int& n2) {
+    for (int k = 0; k < 2 && n2 == 1; ++k) {
+        n2 = n1;
+        n1 = n0;
+        n0 = 1;
+    }
+}
+
+static int launch_copy_inner(const double* A, int n0, int n1, int n2, double* G, long long G1, long long G2,
+                             long long c0, long long c1, long long c2, cudaStream_t st) {
+    const int o0 = n0 > 2, o1 = n1 > 2, o2 = n2 > 2;
+    const int m0 = n0 - 2 * o0, m1 = n1 - 2 * o1, m2 = n2 - 2 * o2;
+    const long long rows = (long long)m0 * m1;
+    long long grid = rows;
+    const long long cap = (long long)igg::sm_count() * 8;
+    if (grid > cap) grid = cap;
+    if (grid < 1) grid = 1;
+    copy_inner_rows_kernel<<<(int)grid, CIR_THREADS, 0, st>>>(A, n1, n2, m1, m2, o0, o1, o2, G, G1, G2, c0 * m0, c1 * m1,
+                                                           c2 * m2, rows);
+    return 0;
 }
 
 // ---- max / sum reduction ----------------------------------------------------------------------------
@@ -203,11 +267,28 @@ int igg_unpack_plane(double* A, int n0, int n1, int n2, int dim, int idx, const 
 
 int igg_extract_inner(const double* A, int n0, int n1, int n2, double* out, void* stream) {
     IGG_REQUIRE(A && out && n0 > 0 && n1 > 0 && n2 > 0, "igg_extract_inner: bad arguments");
-    const int o0 = n0 > 2, o1 = n1 > 2, o2 = n2 > 2;
-    const int m0 = n0 - 2 * o0, m1 = n1 - 2 * o1, m2 = n2 - 2 * o2;
-    const size_t count = (size_t)m0 * m1 * m2;
-    extract_inner_kernel<<<grid_for(count, 256), 256, 0, (cudaStream_t)stream>>>(A, n0, n1, n2, m0, m1, m2, o0, o1,
-                                                                                o2, out);
+    canonical_shape(n0, n1, n2);
+    const int m1 = n1 - 2 * (n1 > 2), m2 = n2 - 2 * (n2 > 2);
+    launch_copy_inner(A, n0, n1, n2, out, m1, m2, 0, 0, 0, (cudaStream_t)stream);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+int igg_gather_inner(const double* A, int n0, int n1, int n2, double* G, int d0, int d1, int d2, int c0, int c1,
+                     int c2, void* stream) {
+    IGG_REQUIRE(A && G && n0 > 0 && n1 > 0 && n2 > 0, "igg_gather_inner: bad arguments");
+    IGG_REQUIRE(d0 >= 1 && d1 >= 1 && d2 >= 1 && c0 >= 0 && c0 < d0 && c1 >= 0 && c1 < d1 && c2 >= 0 && c2 < d2,
+                "igg_gather_inner: block coordinates (%d,%d,%d) outside the process grid %d x %d x %d", c0, c1, c2, d0,
+                d1, d2);
+    // singleton dimensions travel with their process-grid entries
+    for (int k = 0; k < 2 && n2 == 1; ++k) {
+        IGG_REQUIRE(d2 == 1, "igg_gather_inner: a dimension of size 1 cannot be decomposed");
+        n2 = n1; n1 = n0; n0 = 1;
+        d2 = d1; d1 = d0; d0 = 1;
+        c2 = c1; c1 = c0; c0 = 0;
+    }
+    const long long m1 = n1 - 2 * (n1 > 2), m2 = n2 - 2 * (n2 > 2);
+    launch_copy_inner(A, n0, n1, n2, G, m1 * d1, m2 * d2, c0, c1, c2, (cudaStream_t)stream);
     IGG_LAUNCH_CHECK();
     return 0;
 }

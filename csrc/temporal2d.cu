@@ -100,6 +100,64 @@ struct T2Acc {            // running diagnostics of a thread
     double d1max, d1sum, d2max, d2sum;
 };
 
+// Step 1 of one block for one thread: mid rows rg*RPT ... rg*RPT+RPT-1.  EDGE = the block may contain rows outside the
+// item's own output range [x_lo, x_hi] (first block and the last two): only then are rows tested one by one.
+template <int SRB, int RPT, bool DIAG, bool EDGE>
+__device__ __forceinline__ void t2_lean_step1(uint32_t pa, uint32_t pb, uint32_t plast, uint32_t pc, uint32_t pm,
+                                              const Phys& ph1, int xr0, int x_lo, int x_hi, double& imax, double& isum) {
+    constexpr uint32_t ROWB = BW * 8;
+    d2 a = lds128(pa);
+    d2 bb = lds128(pb);
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) {
+        const d2 c = lds128(r + 1 < RPT ? pb + (r + 1) * ROWB : plast);
+        const double bl = lds64(pb + r * ROWB - 8);
+        const double br = lds64(pb + r * ROWB + 16);
+        const d2 cc = lds128(pc + r * ROWB);
+        const double mA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph1);
+        const double mB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph1);
+        sts128(pm + r * ROWB, mA, mB);
+        if (DIAG) {
+            if (!EDGE || (xr0 + r >= x_lo && xr0 + r <= x_hi)) {
+                imax = fmax(imax, fmax(mA, mB));
+                isum += mA + mB;
+            }
+        }
+        a = bb;
+        bb = c;
+    }
+}
+
+// Step 2 of one block for one thread: output rows (xb - 1 + rg*RPT + r) from the mid rows around them.
+template <int SRB, int RPT, bool DIAG, bool EDGE>
+__device__ __forceinline__ void t2_lean_step2(uint32_t mm2, uint32_t mm1, uint32_t m0, uint32_t cm1, uint32_t c0,
+                                              const Phys& ph2, double* __restrict__ out, int ny, bool pair_ok, int x,
+                                              int x_lo, int x_hi, double& imax, double& isum) {
+    constexpr uint32_t ROWB = BW * 8;
+    d2 a = lds128(mm2);
+    d2 bb = lds128(mm1);
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) {
+        const uint32_t rc = r == 0 ? mm1 : m0 + (r - 1) * ROWB;        // row of the output cell
+        const d2 c = lds128(m0 + r * ROWB);
+        const double bl = lds64(rc - 8);
+        const double br = lds64(rc + 16);
+        const d2 cc = lds128(r == 0 ? cm1 : c0 + (r - 1) * ROWB);
+        const double oA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph2);
+        const double oB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph2);
+        const bool row_ok = !EDGE || (x + r >= x_lo && x + r <= x_hi);
+        if (pair_ok && row_ok) st_cs_f64x2(out + (size_t)r * ny, oA, oB);
+        if (DIAG) {
+            if (row_ok) {
+                imax = fmax(imax, fmax(oA, oB));
+                isum += oA + oB;
+            }
+        }
+        a = bb;
+        bb = c;
+    }
+}
+
 template <int SRB, int RPT, bool DIAG>
 __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict__ T2, int ny, const Phys& ph1,
                                               const Phys& ph2, uint32_t sT, uint32_t sC, uint32_t sM, uint32_t fullT,
@@ -112,6 +170,9 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
     const bool lane0 = (threadIdx.x & 31) == 0;
     const bool pair_ok = cp >= 1 && cp <= NPAIR - 2;
     const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;
+    // diagnostics of this item: folded without any per-cell column test (the two garbage column pairs of the box
+    // accumulate garbage) and merged into the thread's running values at the end only where the pair is valid
+    double i1max = -INFINITY, i1sum = 0.0, i2max = -INFINITY, i2sum = 0.0;
     // slots and parities of block 0
     uint32_t ts = tq % SNT, tph = (tq / SNT) & 1u;
     uint32_t cs = cq % SNC, cph = (cq / SNC) & 1u;
@@ -125,6 +186,7 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
         const uint32_t tn = (ts + 1) & (SNT - 1);
         const uint32_t tnph = tn == 0 ? tph ^ 1u : tph;
         const bool has_next = b + 1 < it.nbi;
+        const bool edge = b == 0 || b + 2 >= it.nbi;       // rows outside [x_lo, x_hi] exist only in these blocks
         if (has_next) mbar_wait_u32(fullT + tn * 8, tnph);
         mbar_wait_u32(fullC + cs * 8, cph);
         const uint32_t tc = sT + ts * BLKB, tp = sT + tprev * BLKB, tnx = sT + (has_next ? tn : ts) * BLKB;
@@ -133,28 +195,12 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
         // ---- step 1: mid rows rg*RPT ... rg*RPT+RPT-1 of block b
         {
             const uint32_t pb = tc + myB;
-            d2 a = lds128(rg == 0 ? tp + (SRB - 1) * ROWB + colB : pb - ROWB);
-            d2 bb = lds128(pb);
+            const uint32_t pa = rg == 0 ? tp + (SRB - 1) * ROWB + colB : pb - ROWB;
             const uint32_t plast = rg == NRG - 1 ? tnx + colB : pb + RPT * ROWB;
-#pragma unroll
-            for (int r = 0; r < RPT; ++r) {
-                const d2 c = lds128(r + 1 < RPT ? pb + (r + 1) * ROWB : plast);
-                const double bl = lds64(pb + r * ROWB - 8);
-                const double br = lds64(pb + r * ROWB + 16);
-                const d2 cc = lds128(cc_ + myB + r * ROWB);
-                const double mA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph1);
-                const double mB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph1);
-                sts128(mc + myB + r * ROWB, mA, mB);
-                if (DIAG) {
-                    const int xr = x + 1 + r;          // global row of this mid value
-                    if (pair_ok && xr >= x_lo && xr <= x_hi) {
-                        acc.d1max = fmax(acc.d1max, fmax(mA, mB));      // one dependent op per row on each accumulator
-                        acc.d1sum += mA + mB;
-                    }
-                }
-                a = bb;
-                bb = c;
-            }
+            if (edge)
+                t2_lean_step1<SRB, RPT, DIAG, true>(pa, pb, plast, cc_ + myB, mc + myB, ph1, x + 1, x_lo, x_hi, i1max, i1sum);
+            else
+                t2_lean_step1<SRB, RPT, DIAG, false>(pa, pb, plast, cc_ + myB, mc + myB, ph1, x + 1, x_lo, x_hi, i1max, i1sum);
         }
         __syncwarp();
         if (lane0 && b > 0) mbar_arrive_u32(emptyT + tprev * 8);      // T block b-1 is done
@@ -165,28 +211,10 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
             const uint32_t mm1 = rg == 0 ? mp + (SRB - 1) * ROWB + colB : m0 - ROWB;       // row rg*RPT - 1
             const uint32_t mm2 = rg == 0 ? mp + (SRB - 2) * ROWB + colB : m0 - 2 * ROWB;   // row rg*RPT - 2
             const uint32_t cm1 = rg == 0 ? cpv + (SRB - 1) * ROWB + colB : cc_ + myB - ROWB;
-            d2 a = lds128(mm2);
-            d2 bb = lds128(mm1);
-#pragma unroll
-            for (int r = 0; r < RPT; ++r) {
-                const uint32_t rc = r == 0 ? mm1 : m0 + (r - 1) * ROWB;        // row of the output cell
-                const d2 c = lds128(m0 + r * ROWB);
-                const double bl = lds64(rc - 8);
-                const double br = lds64(rc + 16);
-                const d2 cc = lds128(r == 0 ? cm1 : cc_ + myB + (r - 1) * ROWB);
-                const double oA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph2);
-                const double oB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph2);
-                const int xr = x + r;
-                if (pair_ok && xr >= x_lo && xr <= x_hi) {
-                    st_cs_f64x2(out + (size_t)r * ny, oA, oB);
-                    if (DIAG) {
-                        acc.d2max = fmax(acc.d2max, fmax(oA, oB));
-                        acc.d2sum += oA + oB;
-                    }
-                }
-                a = bb;
-                bb = c;
-            }
+            if (edge)
+                t2_lean_step2<SRB, RPT, DIAG, true>(mm2, mm1, m0, cm1, cc_ + myB, ph2, out, ny, pair_ok, x, x_lo, x_hi, i2max, i2sum);
+            else
+                t2_lean_step2<SRB, RPT, DIAG, false>(mm2, mm1, m0, cm1, cc_ + myB, ph2, out, ny, pair_ok, x, x_lo, x_hi, i2max, i2sum);
         }
         __syncwarp();
         if (lane0 && b > 0) mbar_arrive_u32(emptyC + cprev * 8);      // Cp block b-1 is done
@@ -201,6 +229,12 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
     if (lane0) {
         mbar_arrive_u32(emptyT + tprev * 8);
         mbar_arrive_u32(emptyC + cprev * 8);
+    }
+    if (DIAG && pair_ok) {
+        acc.d1max = fmax(acc.d1max, i1max);
+        acc.d1sum += i1sum;
+        acc.d2max = fmax(acc.d2max, i2max);
+        acc.d2sum += i2sum;
     }
 }
 

@@ -246,6 +246,12 @@ int igg_pack_plane(const double* A, int n0, int n1, int n2, int dim, int idx, do
 int igg_unpack_plane(double* A, int n0, int n1, int n2, int dim, int idx, const double* buf, void* stream);
 /* interior extraction A[1:-1,...] -> dense buffer (reference scripts/diffusion_2D_ap.jl:45) */
 int igg_extract_inner(const double* A, int n0, int n1, int n2, double* out, void* stream);
+/* gather! without host staging (reference scripts/diffusion_2D_ap.jl:45-46: Array(T[2:end-1,2:end-1]) then gather!):
+ * the halo-free interior of A is stored as the block with Cartesian coordinates (c0,c1,c2) of the global array G,
+ * whose shape is (m0*d0, m1*d1, m2*d2) with m = the interior shape and (d0,d1,d2) the process grid.  G is normally a
+ * peer-mapped pointer into the ROOT rank's memory: every rank's tile crosses NVLink once, as 16-byte stores. */
+int igg_gather_inner(const double* A, int n0, int n1, int n2, double* G, int d0, int d1, int d2, int c0, int c1,
+                     int c2, void* stream);
 
 /* ---- peer-memory fabric (replaces GPU-aware MPI, reference scripts/rocmaware_test_selectdevice.jl:15-22)
  * Allocations are plain cudaMalloc blocks that can be exported with CUDA IPC and mapped by the

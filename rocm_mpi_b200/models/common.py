@@ -105,16 +105,24 @@ def visualise_2d(s: Setup, T: torch.Tensor, variant: str, res: RunResult) -> Non
     """Strip halo, gather to rank 0, write PNG + raw dump (reference ``scripts/diffusion_2D_ap.jl:45-47``)."""
     cfg = s.cfg
     g = global_grid()
-    T_nh = inner_to_host(T)
-    T_v = None
-    if g.me == 0:
-        T_v = torch.zeros((cfg.nx - 2) * s.dims[0], (cfg.ny - 2) * s.dims[1], dtype=T.dtype)
-    gather(T_nh, T_v)
+    from ..parallel.gather import device_gather_ok, gather_interior_device
+    T_dev = None
+    if device_gather_ok(T):
+        # tiles go straight into the root GPU's memory; the heat map is rasterised there, and only the raw dump
+        # needs the field on the host
+        T_dev = gather_interior_device(T)
+        T_v = T_dev.cpu() if g.me == 0 else None
+    else:
+        T_nh = inner_to_host(T)
+        T_v = None
+        if g.me == 0:
+            T_v = torch.zeros((cfg.nx - 2) * s.dims[0], (cfg.ny - 2) * s.dims[1], dtype=T.dtype)
+        gather(T_nh, T_v)
     if g.me == 0:
         res.T_v = T_v
         res.max_T = float(T_v.max())
         base = os.path.join(cfg.outdir, output_name(variant, s.nprocs, nx_g(), ny_g()))
-        res.png = save_heatmap(base + ".png", T_v, title=f"{variant}: T after {cfg.nt} steps, "
-                               f"{s.nprocs} ranks {s.dims[0]}x{s.dims[1]}")
+        res.png = save_heatmap(base + ".png", T_dev if T_dev is not None else T_v,
+                               title=f"{variant}: T after {cfg.nt} steps, {s.nprocs} ranks {s.dims[0]}x{s.dims[1]}")
         res.raw, _ = save_raw(base, T_v, {"variant": variant, "nprocs": s.nprocs, "dims": list(s.dims),
                                            "nx_g": nx_g(), "ny_g": ny_g(), "nt": cfg.nt})

@@ -37,77 +37,104 @@ from ..parallel.halo import default_transport
 from ..utils.config import DiffusionConfig, add_config_args, config_from_args
 from .common import detach_local, RunResult, initial_condition_2d, log0, setup_2d, visualise_2d
 
-__all__ = ["diffusion2D_kp", "main"]
+__all__ = ["diffusion2D_kp", "KPThree", "main"]
+
+
+class KPThree:
+    """The literal kp time loop on one rank: ``Flux!`` / ``Residual!`` / ``Update!`` launches per step
+    (reference ``scripts/diffusion_2D_kp.jl:87-92``) with the halo handled by ``transport`` (see module docstring).
+    ``step(n)`` queues ``n`` steps; ``finish()`` waits for the last pushes.  Used by the application below and by
+    ``benchmarks/small_grid_latency.py``."""
+
+    def __init__(self, nx: int, ny: int, dx: float, dy: float, dt: float, lam: float, Cp0: float, T0: torch.Tensor,
+                 transport: str, fused: bool = True) -> None:
+        g = global_grid()
+        dev, f64 = T0.device, torch.float64
+        self.g, self.nx, self.ny, self.dt, self.lam = g, nx, ny, dt, lam
+        self._dx, self._dy = 1.0 / dx, 1.0 / dy
+        self.on_gpu = dev.type == "cuda"
+        if self.on_gpu:
+            native.require()
+        self.transport = transport
+        self.comm_needed = g.nprocs > 1 or any(g.periods)
+        self.fused_push = self.on_gpu and transport == "peer" and fused and self.comm_needed
+        # Array initializations (reference scripts/diffusion_2D_kp.jl:73-78)
+        self.dTdt = torch.zeros(nx - 2, ny - 2, dtype=f64, device=dev)
+        self.qx = torch.zeros(nx - 1, ny - 2, dtype=f64, device=dev)
+        self.qy = torch.zeros(nx - 2, ny - 1, dtype=f64, device=dev)
+        self.Cp = Cp0 * torch.ones(nx, ny, dtype=f64, device=dev)
+        if self.fused_push:
+            self.T = fabric_zeros((nx, ny))
+            self.T.copy_(T0)
+        else:
+            self.T = T0
+        self.cpu_native = (not self.on_gpu) and native.loaded() and self.T.is_contiguous()
+        self.plan = None
+        if self.fused_push:
+            self.fab = get_fabric()
+            self.plan = PushPlan(self.T)
+            self.bar_bank = self.fab.new_bank()
+            self.bar_epoch = 0
+            self.plan.begin()
+
+    def step(self, n: int = 1) -> None:
+        T, Cp, qx, qy, dTdt = self.T, self.Cp, self.qx, self.qy, self.dTdt
+        for _ in range(int(n)):
+            if self.on_gpu:
+                if self.fused_push:
+                    # neighbours' Update! of the previous step has landed in my halo cells
+                    sync = self.fab.sync_struct(self.plan.bank, self.plan.epoch)
+                    native._check(self.fab.lib.igg_wait_epoch(C.byref(sync), native._stream()))
+                native.flux2d(qx, qy, T, self.lam, self._dx, self._dy)
+                native.residual2d(dTdt, qx, qy, Cp, self._dx, self._dy)
+                if self.fused_push:
+                    # every neighbour has finished reading its halo cells (its Flux!) before I overwrite them
+                    self.bar_epoch += 1
+                    bsync = self.fab.sync_struct(self.bar_bank, self.bar_epoch)
+                    native._check(self.fab.lib.igg_neighbor_barrier(C.byref(bsync), native._stream()))
+                    native.update2d(T, dTdt, self.dt, push=self.plan.next(T))
+                else:
+                    native.update2d(T, dTdt, self.dt)
+                    if self.comm_needed:
+                        update_halo(T, transport=self.transport)
+            else:
+                if self.cpu_native:            # the three kernels as OpenMP loop nests (csrc/cpu_oracle.cpp)
+                    native.cpu_kp_step(T, Cp, qx, qy, dTdt, self.lam, self.dt, self._dx, self._dy)
+                else:
+                    ref.kp_step(T, Cp, qx, qy, dTdt, self.lam, self.dt, self._dx, self._dy)
+                if self.comm_needed:
+                    update_halo(T)
+
+    def finish(self) -> None:
+        if self.plan is not None:
+            self.plan.finish()
+
+    def close(self) -> None:
+        """Collective: give the flag banks back (a sweep that builds several steppers in one grid)."""
+        if self.plan is not None:
+            self.plan.close()
+            self.fab.release_bank(self.bar_bank)
+            self.plan = None
 
 
 def diffusion2D_kp(cfg: DiffusionConfig = None, finalize: bool = True) -> RunResult:
     cfg = cfg or DiffusionConfig()
     s = setup_2d(cfg)
     g = global_grid()
-    dev, f64 = s.device, torch.float64
-    nx, ny = cfg.nx, cfg.ny
+    dev = s.device
     on_gpu = dev.type == "cuda"
-    if on_gpu:
-        native.require()
-    _dx, _dy = 1.0 / s.dx, 1.0 / s.dy
     transport = cfg.transport or default_transport(torch.empty(0, device=dev))
-    comm_needed = g.nprocs > 1 or any(g.periods)
     if cfg.kp_path not in ("three", "persistent", "resident", "auto"):
         raise ValueError("kp_path must be three | persistent | resident | auto")
     if on_gpu and cfg.kp_path != "three":
         return _single_launch(cfg, s, finalize)
-    fused_push = on_gpu and transport == "peer" and cfg.fused and comm_needed
-    # Array initializations (reference scripts/diffusion_2D_kp.jl:73-78)
-    dTdt = torch.zeros(nx - 2, ny - 2, dtype=f64, device=dev)
-    qx = torch.zeros(nx - 1, ny - 2, dtype=f64, device=dev)
-    qy = torch.zeros(nx - 2, ny - 1, dtype=f64, device=dev)
-    Cp = cfg.Cp0 * torch.ones(nx, ny, dtype=f64, device=dev)
-    T0 = initial_condition_2d(s)
-    if fused_push:
-        T = fabric_zeros((nx, ny))
-        T.copy_(T0)
-    else:
-        T = T0
     n0 = native.launch_count()
-    cpu_native = (not on_gpu) and native.loaded() and T.is_contiguous()
-
-    plan = None
-    if fused_push:
-        fab = get_fabric()
-        plan = PushPlan(T)
-        bar_bank = fab.new_bank()
-        bar_epoch = 0
-        plan.begin()
-        lib = fab.lib
+    kp = KPThree(cfg.nx, cfg.ny, s.dx, s.dy, s.dt, cfg.lam, cfg.Cp0, initial_condition_2d(s), transport, cfg.fused)
     log0("Starting the time loop ...", end="")
-    for _ in range(int(cfg.nt)):
-        if on_gpu:
-            if fused_push:
-                # neighbours' Update! of the previous step has landed in my halo cells
-                sync = fab.sync_struct(plan.bank, plan.epoch)
-                native._check(lib.igg_wait_epoch(C.byref(sync), native._stream()))
-            native.flux2d(qx, qy, T, cfg.lam, _dx, _dy)
-            native.residual2d(dTdt, qx, qy, Cp, _dx, _dy)
-            if fused_push:
-                # every neighbour has finished reading its halo cells (its Flux!) before I overwrite them
-                bar_epoch += 1
-                bsync = fab.sync_struct(bar_bank, bar_epoch)
-                native._check(lib.igg_neighbor_barrier(C.byref(bsync), native._stream()))
-                native.update2d(T, dTdt, s.dt, push=plan.next(T))
-            else:
-                native.update2d(T, dTdt, s.dt)
-                if comm_needed:
-                    update_halo(T, transport=transport)
-        else:
-            if cpu_native:                 # the three kernels as OpenMP loop nests (csrc/cpu_oracle.cpp)
-                native.cpu_kp_step(T, Cp, qx, qy, dTdt, cfg.lam, s.dt, _dx, _dy)
-            else:
-                ref.kp_step(T, Cp, qx, qy, dTdt, cfg.lam, s.dt, _dx, _dy)
-            if comm_needed:
-                update_halo(T)
-    if plan is not None:
-        plan.finish()
+    kp.step(int(cfg.nt))
+    kp.finish()
     log0("done")
+    T = kp.T
     res = RunResult("kp", s.me, s.nprocs, s.dims, int(cfg.nt), T_local=T, launches=native.launch_count() - n0)
     if cfg.do_vis:
         visualise_2d(s, T, "kp", res)

@@ -149,12 +149,16 @@ def diffusion3D(cfg: DiffusionConfig = None, finalize: bool = True, mode: Option
     res = RunResult("3D", me, nprocs, dims, nt, wtime=wtime, t_eff=T_eff, T_local=s.T,
                     launches=native.launch_count() - n0)
     if cfg.do_vis:
-        from ..parallel.gather import inner_to_host
-        T_nh = inner_to_host(s.T)
-        T_v = None
-        if me == 0:
-            T_v = torch.zeros(tuple((n - 2) * d for n, d in zip(s.shape, dims)), dtype=torch.float64)
-        gather(T_nh, T_v)
+        from ..parallel.gather import device_gather_ok, gather_interior_device, inner_to_host
+        if device_gather_ok(s.T):          # tiles stored into the root GPU's memory (3-D blocks, 16-byte rows)
+            G = gather_interior_device(s.T)
+            T_v = G.cpu() if me == 0 else None
+        else:
+            T_nh = inner_to_host(s.T)
+            T_v = None
+            if me == 0:
+                T_v = torch.zeros(tuple((n - 2) * d for n, d in zip(s.shape, dims)), dtype=torch.float64)
+            gather(T_nh, T_v)
         if me == 0:
             res.T_v, res.max_T = T_v, float(T_v.max())
             base = os.path.join(cfg.outdir, output_name("3D", nprocs, nx_g(), ny_g(), nz_g()))

@@ -103,6 +103,7 @@ def _declare(lib) -> None:
         "igg_ipc_open": ([vp, C.POINTER(vp)], i),
         "igg_ipc_close": ([vp], i),
         "igg_can_access_peer": ([i, i, C.POINTER(i)], i),
+        "igg_gather_inner": ([vp, i, i, i, vp, i, i, i, i, i, i, vp], i),
         "igg_halo_exchange_peer": ([vp, i, C.POINTER(HaloSync), vp], i),
         "igg_halo_exchange_peer_ex": ([vp, i, C.POINTER(HaloSync), i, vp], i),
         "igg_neighbor_barrier": ([C.POINTER(HaloSync), vp], i),
@@ -499,6 +500,16 @@ def extract_inner(A, out=None) -> torch.Tensor:
         out = torch.empty(shape, dtype=A.dtype, device=A.device)
     _check(require().igg_extract_inner(_f64(A), n0, n1, n2, _f64(out), _stream()))
     return out
+
+
+def gather_inner(A: torch.Tensor, G_ptr: int, dims: Sequence[int], coords: Sequence[int]) -> None:
+    """Store the halo-free interior of ``A`` as block ``coords`` of the global array at ``G_ptr`` (usually a
+    peer-mapped pointer into the root's memory); ``igg_gather_inner``."""
+    n0, n1, n2 = _shape3(A)
+    d = list(dims) + [1] * (3 - len(dims))
+    c = list(coords) + [0] * (3 - len(coords))
+    _check(require().igg_gather_inner(_f64(A), n0, n1, n2, G_ptr, int(d[0]), int(d[1]), int(d[2]), int(c[0]),
+                                      int(c[1]), int(c[2]), _stream()))
 
 
 # ---- diagnostics ------------------------------------------------------------------------------------

@@ -82,6 +82,7 @@ class Fabric:
         # the neighbours keep storing into freed memory)
         self._registered: Dict[int, torch.Tensor] = {}
         self._free_banks: List[int] = []
+        self._root_bufs: Dict[tuple, tuple] = {}        # (shape, dtype, root) -> (tensor on root | None, my pointer)
         self.neighbors = neighbor_offsets(g)
         self.neighbor_ranks = sorted({r for _, r in self.neighbors})
         self._next_bank = 0
@@ -182,6 +183,51 @@ class Fabric:
                 self.lib.igg_ipc_close(base)
         self._forget_tables(key)
         self.g.comm.barrier()
+
+    def root_buffer(self, shape: Sequence[int], dtype: torch.dtype = torch.float64, root: int = 0):
+        """Collective: a zero-filled buffer that lives on ``root`` only and that EVERY rank can store into.
+
+        Returns ``(tensor, ptr)``: the tensor on ``root`` (``None`` elsewhere) and this rank's pointer to the
+        buffer (peer-mapped off the root).  Used by the device-side ``gather``: the gathered field exists once,
+        in the root's memory, and the other ranks write their tiles straight into it.  Cached per
+        ``(shape, dtype, root)``; released by :meth:`close`."""
+        shape = tuple(int(x) for x in shape)
+        key = (shape, dtype, int(root))
+        hit = self._root_bufs.get(key)
+        if hit is not None:
+            return hit
+        g = self.g
+        t, info = None, None
+        if g.me == root:
+            numel = 1
+            for x in shape:
+                numel *= x
+            nbytes = max(numel * torch.empty((), dtype=dtype).element_size(), 16)
+            ptr = C.c_void_p()
+            native._check(self.lib.igg_fabric_alloc(nbytes, C.byref(ptr)))
+            self._owned[ptr.value] = nbytes
+            blk = _DeviceBlock(ptr.value, shape, _TYPESTR[dtype])
+            t = torch.as_tensor(blk, device=g.device)
+            self._keepalive.append(blk)
+            if g.nprocs > 1:
+                handle = (C.c_ubyte * 64)()
+                off = C.c_uint64(0)
+                native._check(self.lib.igg_ipc_export(ptr.value, handle, C.byref(off)))
+                info = (bytes(handle), int(off.value))
+        my_ptr = t.data_ptr() if t is not None else 0
+        if g.nprocs > 1:
+            infos = g.comm.allgather_object(info)
+            if g.me != root:
+                h, o = infos[root]
+                base = self._opened.get(h)
+                if base is None:
+                    out = C.c_void_p()
+                    native._check(self.lib.igg_ipc_open(h, C.byref(out)))
+                    base = out.value
+                    self._opened[h] = base
+                my_ptr = base + o
+        self._root_bufs[key] = (t, my_ptr)
+        return t, my_ptr
 
     def _forget_tables(self, data_ptr: int) -> None:
         eng = self.g.cache.get(("halo", "peer"))
@@ -285,6 +331,7 @@ class Fabric:
         self._peer_ptrs.clear()
         self._handles.clear()
         self._registered.clear()
+        self._root_bufs.clear()
         self.g.comm.barrier()                       # every rank has dropped its mappings
         for ptr in list(self._owned):
             self.lib.igg_fabric_free(ptr)

@@ -15,7 +15,7 @@ import torch
 from .grid import global_grid
 from .topology import cart_coords
 
-__all__ = ["gather", "inner", "inner_to_host", "gather_interior"]
+__all__ = ["gather", "inner", "inner_to_host", "gather_interior", "gather_interior_device", "device_gather_ok"]
 
 
 def inner(A: torch.Tensor) -> torch.Tensor:
@@ -71,8 +71,14 @@ def inner_to_host(A: torch.Tensor) -> torch.Tensor:
 
 
 def gather_interior(A: torch.Tensor, root: int = 0) -> Optional[torch.Tensor]:
-    """Convenience: strip the halo, gather, and return the global array on the root."""
+    """Convenience: strip the halo, gather, and return the global array (a HOST tensor) on the root.
+
+    CUDA fields on one node take the device path (tiles stored into the root's memory over NVLink, then one
+    device-to-host copy on the root); everything else is staged through the host as the reference does."""
     g = global_grid()
+    if device_gather_ok(A) and all(g.nxyz[d] > 2 or g.dims[d] == 1 for d in range(A.dim())):
+        G = gather_interior_device(A, root)
+        return G.cpu() if G is not None else None
     blk = inner_to_host(A)
     out = None
     if g.me == root:
@@ -80,3 +86,40 @@ def gather_interior(A: torch.Tensor, root: int = 0) -> Optional[torch.Tensor]:
                           dtype=A.dtype)
     gather(blk, out, root)
     return out
+
+
+def device_gather_ok(A: torch.Tensor) -> bool:
+    """Can ``gather_interior_device`` serve this field?  (CUDA fp64, contiguous, native library, one node.)"""
+    if not (A.is_cuda and A.dtype == torch.float64 and A.is_contiguous()):
+        return False
+    from ..ops import native
+    if not native.available():
+        return False
+    from .comm import spans_nodes
+    return not spans_nodes()
+
+
+def gather_interior_device(A: torch.Tensor, root: int = 0, sync: bool = True) -> Optional[torch.Tensor]:
+    """``gather!`` of the halo-free interior WITHOUT host staging: returns the global array as a device tensor
+    on ``root`` (``None`` elsewhere).
+
+    The reference copies every rank's interior to the host and lets MPI collect the blocks
+    (``Array(T[2:end-1,2:end-1])`` then ``gather!``, ``scripts/diffusion_2D_ap.jl:45-46``; 1.2 GB per rank in
+    the perf run, ``scripts/diffusion_2D_perf.jl:59-63``).  Here the global array exists once, in the root's
+    memory; every rank runs ONE kernel that stores its tile into it at its Cartesian position -- through a
+    peer-mapped pointer over NVLink for the other ranks (``igg_gather_inner``).  Collective.  The returned tensor
+    is a cached buffer of the fabric: the next ``gather_interior_device`` of the same shape overwrites it."""
+    from ..ops import native
+    from .fabric import get_fabric
+    g = global_grid()
+    fab = get_fabric(g)
+    fab.check_all_errors()                  # never gather a field whose halo exchange timed out
+    nd = A.dim()
+    m = tuple(s - 2 if s > 2 else s for s in A.shape)
+    gshape = tuple(m[d] * g.dims[d] for d in range(nd))
+    G, ptr = fab.root_buffer(gshape, A.dtype, root)
+    native.gather_inner(A, ptr, g.dims[:nd], g.coords[:nd])
+    if sync:
+        torch.cuda.current_stream().synchronize()
+        g.comm.barrier()                    # every tile has landed in the root's buffer
+    return G if g.me == root else None

@@ -102,14 +102,28 @@ def save_heatmap(path: str, field, size: Tuple[int, int] = (600, 400), vmin=None
                  title: Optional[str] = None) -> str:
     """Write the heat map of ``field[ix, iy]`` (x to the right, y up, like ``heatmap(transpose(T_v))``)."""
     W, H = size
-    a = field.detach().cpu() if torch.is_tensor(field) else torch.as_tensor(np.asarray(field))
-    lo = float(a.min()) if vmin is None else vmin
-    hi = float(a.max()) if vmax is None else vmax
+    left, right, top, bottom = 50, 110, 25, 35
+    pw, ph = W - left - right, H - top - bottom
+    nxv, nyv = int(field.shape[0]), int(field.shape[1])
+    if torch.is_tensor(field) and field.is_cuda:
+        # a gathered field can be many GB (12286^2 per rank in the reference's perf run): take min / max on the
+        # device and colour-map only the pw x ph cells the picture shows (same nearest-neighbour picks as
+        # _resize_nearest makes on the full image), instead of moving the whole field to the host
+        lo_t, hi_t = torch.aminmax(field.detach())
+        lo = float(lo_t) if vmin is None else vmin
+        hi = float(hi_t) if vmax is None else vmax
+        if nxv > pw or nyv > ph:
+            xs = (torch.arange(pw) * nxv // pw).clamp(0, nxv - 1)
+            ys = (torch.arange(ph) * nyv // ph).clamp(0, nyv - 1)
+            yidx = (nyv - 1) - ys.flip(0)
+            field = field.detach().index_select(0, xs.to(field.device)).index_select(1, yidx.to(field.device))
+    else:
+        a = field.detach() if torch.is_tensor(field) else torch.as_tensor(np.asarray(field))
+        lo = float(a.min()) if vmin is None else vmin
+        hi = float(a.max()) if vmax is None else vmax
     rgb = colorize(field, lo, hi)                 # [ix, iy, 3]
     img = np.flipud(np.transpose(rgb, (1, 0, 2)))  # rows = y (up), cols = x
     canvas = np.full((H, W, 3), 255, dtype=np.uint8)
-    left, right, top, bottom = 50, 110, 25, 35
-    pw, ph = W - left - right, H - top - bottom
     canvas[top:top + ph, left:left + pw] = _resize_nearest(img, ph, pw)
     # frame
     canvas[top - 1, left - 1:left + pw + 1] = 0
@@ -125,7 +139,6 @@ def save_heatmap(path: str, field, size: Tuple[int, int] = (600, 400), vmin=None
     canvas[top - 1:top + ph + 1, bx0 - 1] = 0
     canvas[top - 1:top + ph + 1, bx0 + bw] = 0
     labels = []
-    nxv, nyv = int(a.shape[0]), int(a.shape[1])
     for k in range(5):
         fx = k / 4.0
         px = left + int(fx * (pw - 1))

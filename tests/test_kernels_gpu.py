@@ -235,3 +235,21 @@ def test_strip_kernel_agrees_with_direct_kernel_at_bench_like_size():
     native.diffusion2d_step(B, T, Cp, 1.0, 1e-3, 2.0, 3.0, variant="direct")
     assert float((A - B).abs().max()) < 1e-13
     assert torch.equal(A[0], T[0]) and torch.equal(A[:, -1], T[:, -1])
+
+
+@pytest.mark.parametrize("shape", [(5, 6), (66, 131), (300, 258), (17, 20, 23), (40, 36, 66)])
+def test_extract_inner_and_device_gather_single_rank(shape):
+    """Row-wise interior copy (16-byte stores, 8-byte aligned source): dense extraction and the gather kernel that
+    stores the tile into the (here: own) root buffer -- reference scripts/diffusion_2D_ap.jl:45-46."""
+    import rocm_mpi_b200 as igg
+    from rocm_mpi_b200.parallel.gather import gather_interior_device, inner
+    A = torch.rand(*shape, dtype=torch.float64, device="cuda")
+    want = inner(A).contiguous()
+    assert torch.equal(native.extract_inner(A), want)
+    n = list(shape) + [1] * (3 - len(shape))
+    igg.init_global_grid(n[0], n[1], n[2], quiet=True, init_dist=False)
+    G = gather_interior_device(A)
+    assert tuple(G.shape) == tuple(want.shape) and torch.equal(G, want)
+    G2 = gather_interior_device(A * 2.0)             # cached buffer, second use
+    assert torch.equal(G2, want * 2.0)
+    igg.finalize_global_grid(finalize_dist=False)
