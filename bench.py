@@ -110,18 +110,54 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+class NvlinkCounters:
+    """NVLink payload counters of one GPU (NVML field values, all links summed; KiB resolution).  The bytes that
+    cross NVLink during a timed region, next to the algorithmic halo bytes, are the NVLink side of the fused
+    kernel's roofline; ``None`` where NVML does not expose the counters."""
+
+    def __init__(self, gpu_index: int) -> None:
+        self.h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.ids = [(pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
+                        (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF)]
+            if self.read() is None:
+                self.h = None
+        except Exception:
+            self.h = None
+
+    def read(self):
+        if self.h is None:
+            return None
+        try:
+            v = self.nv.nvmlDeviceGetFieldValues(self.h, self.ids)
+            out = []
+            for x in v:
+                if x.nvmlReturn != 0:
+                    return None
+                out.append(int(x.value.ullVal) * 1024)
+            return out
+        except Exception:
+            return None
+
+
 IMPLS = {"ours": ("fused", "tma", "peer"), "hide": ("hide", "tma", "peer"), "direct": ("fused", "direct", "peer"),
          "temporal": ("temporal", "tma", "peer"), "plain_peer": ("plain", "tma", "peer"),
          "nccl_tma": ("plain", "tma", "nccl"), "nccl": ("plain", "direct", "nccl")}
 DEFAULT_OURS = "temporal"        # what `--kernel auto` resolves to (the faster of the two on B200, see profiles/)
 
 
-def time_steps(s, g, W, K, native, torch):
-    """W untimed + K timed steps of solver ``s``: (ms per step, max over ranks; native launches in the region)."""
+def time_steps(s, g, W, K, native, torch, nvl=None):
+    """W untimed + K timed steps of solver ``s``: (ms per step, max over ranks; native launches in the region;
+    NVLink payload bytes [tx, rx] of this rank's GPU during the region, if ``nvl`` can read them)."""
     s.begin()
     s.step(W)
     g.comm.barrier()
     torch.cuda.synchronize()
+    c0 = nvl.read() if nvl is not None else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n0 = native.launch_count()
     e0.record()
@@ -129,10 +165,12 @@ def time_steps(s, g, W, K, native, torch):
     e1.record()
     torch.cuda.synchronize()
     n1 = native.launch_count()
+    c1 = nvl.read() if nvl is not None else None
     g.comm.barrier()
     ms = g.comm.allreduce_max(e0.elapsed_time(e1)) / K
     s.finish()
-    return ms, int(n1 - n0)
+    link = [c1[0] - c0[0], c1[1] - c0[1]] if (c0 is not None and c1 is not None) else None
+    return ms, int(n1 - n0), link
 
 
 def time_e2e(s, g, W, K, pair, torch):
@@ -280,7 +318,8 @@ def main() -> int:
 
     # ---- device-timed region -------------------------------------------------------------------
     sampler = ClockSampler(g.device.index) if me == 0 else None
-    ms, launches = time_steps(s, g, W, K, native, torch)
+    nvl = NvlinkCounters(g.device.index) if me == 0 else None
+    ms, launches, link_bytes = time_steps(s, g, W, K, native, torch, nvl)
     t_eff = A_eff / (ms * 1e-3)
 
     # ---- end-to-end region ---------------------------------------------------------------------
@@ -305,7 +344,7 @@ def main() -> int:
         for name in ("nccl", "nccl_tma"):
             bm, bv, bt = IMPLS[name]
             sb = Diffusion2D(nx, ny, mode=bm, variant=bv, transport=bt if nprocs > 1 else "peer", b_width=a.b_width)
-            bms, _ = time_steps(sb, g, W, K, native, torch)
+            bms, _, _ = time_steps(sb, g, W, K, native, torch)
             sb.close()
             base[name] = {"ms_per_step": round(bms, 5), "value": round(nprocs * A_eff / (bms * 1e-3), 2)}
 
@@ -325,7 +364,7 @@ def main() -> int:
         except Exception:
             pass
         hbm = peaks.get("hbm_gbs", 6650.0)
-        nvl = 770.0                                   # measured peer copy, GB/s per direction per GPU (profiling recipe)
+        nvl_gbs = 770.0                                # measured peer copy, GB/s per direction per GPU (profiling recipe)
         # bytes this rank sends per step: one edge line per existing face neighbour (+ 8 B per corner); the
         # two-step mode sends a mid line and an edge line per PAIR of steps -- the same per step
         # face neighbours of the busiest rank per dimension: none (dims 1), one (dims 2), two (dims > 2)
@@ -333,7 +372,7 @@ def main() -> int:
         halo_bytes = 8 * (n_face[0] * ny + n_face[1] * nx)
         hbm_term = A_eff / steps_per_pass / hbm * 1e3 if steps_per_pass > 1 else A_eff / hbm * 1e3
         dram_bytes_step = A_eff / steps_per_pass if steps_per_pass > 1 else A_eff
-        nvl_term = halo_bytes / 1e9 / nvl * 1e3
+        nvl_term = halo_bytes / 1e9 / nvl_gbs * 1e3
         roof_ms = max(hbm_term, nvl_term)
         value = round(nprocs * t_eff, 2)
         out = {
@@ -351,12 +390,16 @@ def main() -> int:
                        "steps_per_pass": steps_per_pass,
                        "l2": "inputs exceed L2 (3 x %.2f GiB per GPU per step vs 126 MB)" % (nx * ny * 8 / 2**30)},
             "per_gpu_T_eff": round(t_eff, 2),
-            "roofline": {"hbm_gbs": hbm, "nvlink_gbs_per_dir": nvl,
+            "roofline": {"hbm_gbs": hbm, "nvlink_gbs_per_dir": nvl_gbs,
                          "source": "MEASURED_PEAKS.json" if peaks else "fallback",
                          "fraction_of_hbm_peak": round(t_eff / hbm, 4),
                          "dram_bytes_per_step_algorithmic": int(dram_bytes_step * 1e9),
                          "hbm_term_ms": round(hbm_term, 5), "halo_bytes_per_step": halo_bytes,
                          "nvlink_term_ms": round(nvl_term, 6), "bound": "hbm" if hbm_term >= nvl_term else "nvlink",
+                         "nvlink_measured_bytes_per_step_rank0": ({"tx": link_bytes[0] // K, "rx": link_bytes[1] // K,
+                                                                   "source": "NVML NVLINK_THROUGHPUT_DATA_TX/RX over the "
+                                                                             "device-timed region (payload, KiB counters)"}
+                                                                  if link_bytes is not None else None),
                          "fraction_of_roofline": round(roof_ms / ms, 4),
                          "note": ("T_eff keeps the reference's definition (3 arrays of the grid per STEP, "
                                   "scripts/diffusion_2D_perf.jl:55-57); a two-step pass moves those bytes once per TWO "

@@ -38,22 +38,7 @@ __device__ __forceinline__ void push_cell_2d_to(double* const* peer_dst, int nx,
 }
 
 __device__ __forceinline__ void push_cell_2d(const igg_push2d& ps, int nx, int ny, int x, int y, double v) {
-    const bool xl = (x == 1), xh = (x == nx - 2), yl = (y == 1), yh = (y == ny - 2);
-    if (!(xl | xh | yl | yh)) return;
-#pragma unroll
-    for (int sx = -1; sx <= 1; ++sx) {
-        if ((sx == -1 && !xl) || (sx == 1 && !xh)) continue;
-#pragma unroll
-        for (int sy = -1; sy <= 1; ++sy) {
-            if ((sy == -1 && !yl) || (sy == 1 && !yh)) continue;
-            if (sx == 0 && sy == 0) continue;
-            double* dst = ps.peer_dst[(sx + 1) * 3 + (sy + 1)];
-            if (dst == nullptr) continue;
-            const int dx = (sx == -1) ? nx - 1 : (sx == 1 ? 0 : x);
-            const int dy = (sy == -1) ? ny - 1 : (sy == 1 ? 0 : y);
-            dst[(size_t)dx * ny + dy] = v;
-        }
-    }
+    push_cell_2d_to(ps.peer_dst, nx, ny, x, y, v);
 }
 
 // One thread per CTA, after a CTA-wide barrier that follows the tile's last remote store.
@@ -89,38 +74,17 @@ __device__ __forceinline__ bool wait_faces_2d_epoch(const igg_push2d& ps, bool l
     return any;
 }
 
+// the step's own epoch: what the per-step kernels use (the multi-step kernel passes the epoch of each step)
 __device__ __forceinline__ void signal_edges_2d(const igg_push2d& ps, const int* edge_tiles, bool lo_x,
                                                 bool hi_x, bool lo_y, bool hi_y) {
-    __threadfence_system();
-#pragma unroll
-    for (int sx = -1; sx <= 1; ++sx) {
-        if ((sx == -1 && !lo_x) || (sx == 1 && !hi_x)) continue;
-#pragma unroll
-        for (int sy = -1; sy <= 1; ++sy) {
-            if ((sy == -1 && !lo_y) || (sy == 1 && !hi_y)) continue;
-            if (sx == 0 && sy == 0) continue;
-            const int o = (sx + 1) * 3 + (sy + 1);
-            if (ps.peer_flag[o] == nullptr) continue;
-            const unsigned long long old = atomicAdd((unsigned long long*)ps.my_count[o], 1ull);
-            if ((old + 1ull) % (unsigned long long)edge_tiles[o] == 0ull) {
-                __threadfence_system();
-                st_release_sys(ps.peer_flag[o], ps.epoch);
-            }
-        }
-    }
+    signal_edges_2d_epoch(ps, edge_tiles, lo_x, hi_x, lo_y, hi_y, ps.epoch);
 }
 
 // Before a tile reads halo planes: acquire the previous epoch from the face neighbours it touches.
 // Returns true if any flag was actually acquired.
 __device__ __forceinline__ bool wait_faces_2d(const igg_push2d& ps, bool lo_x, bool hi_x, bool lo_y,
                                               bool hi_y) {
-    const uint64_t want = ps.epoch - 1;
-    bool any = false;
-    if (lo_x && ps.my_flag[0 * 3 + 1]) { wait_flag_ge(ps.my_flag[0 * 3 + 1], want, ps.err_word); any = true; }
-    if (hi_x && ps.my_flag[2 * 3 + 1]) { wait_flag_ge(ps.my_flag[2 * 3 + 1], want, ps.err_word); any = true; }
-    if (lo_y && ps.my_flag[1 * 3 + 0]) { wait_flag_ge(ps.my_flag[1 * 3 + 0], want, ps.err_word); any = true; }
-    if (hi_y && ps.my_flag[1 * 3 + 2]) { wait_flag_ge(ps.my_flag[1 * 3 + 2], want, ps.err_word); any = true; }
-    return any;
+    return wait_faces_2d_epoch(ps, lo_x, hi_x, lo_y, hi_y, ps.epoch - 1);
 }
 
 // ---- 3-D -------------------------------------------------------------------------------------------

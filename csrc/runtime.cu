@@ -94,11 +94,29 @@ int get_tensor_map_f64(const void* base, int rank, const uint64_t* dims, const u
         key.dims[i] = dims[i];
         key.box[i] = box[i];
     }
+    // A time loop asks for the same two to six maps on every launch: a small per-thread table of the most recent
+    // ones answers without hashing or taking the mutex (launch preparation is what bounds small-grid steps).
+    constexpr int RECENT = 8;
+    static thread_local MapKey recent_key[RECENT];
+    static thread_local CUtensorMap recent_map[RECENT];
+    static thread_local int recent_n = 0, recent_next = 0;
+    for (int i = 0; i < recent_n; ++i)
+        if (memcmp(&recent_key[i], &key, sizeof(MapKey)) == 0) {
+            *out = recent_map[i];
+            return 0;
+        }
+    auto remember = [&](const CUtensorMap& m) {
+        recent_key[recent_next] = key;
+        recent_map[recent_next] = m;
+        recent_next = (recent_next + 1) % RECENT;
+        if (recent_n < RECENT) ++recent_n;
+    };
     {
         std::lock_guard<std::mutex> lk(mu);
         auto it = cache.find(key);
         if (it != cache.end()) {
             *out = it->second;
+            remember(it->second);
             return 0;
         }
     }
@@ -134,6 +152,7 @@ int get_tensor_map_f64(const void* base, int rank, const uint64_t* dims, const u
         if (cache.size() > 4096) cache.clear();
         cache[key] = m;
     }
+    remember(m);
     *out = m;
     return 0;
 }

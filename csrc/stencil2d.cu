@@ -120,13 +120,6 @@ __device__ __forceinline__ bool in_frame(const Params& p, int x, int y) {
     return x <= p.bwx || x >= p.nx - 1 - p.bwx || y <= p.bwy || y >= p.ny - 1 - p.bwy;
 }
 
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// barrier among the consumer threads only (the producer warp never joins it)
-__device__ __forceinline__ void consumer_sync(int nthreads) {
-    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
-}
 
 // Fused diagnostic {max, sum}, shared by the tile and the strip kernel: every consumer thread brings its partial;
 // CTA partial -> scratch, the last CTA (ticket) folds all partials in a fixed order (deterministic sum) and

@@ -93,12 +93,6 @@ __device__ __forceinline__ bool writes(const Params3& p, int x, int y, int z) {
 }
 
 // ---- variant 1: 2.5-D TMA kernel ----------------------------------------------------------------------
-__device__ __forceinline__ void mbar_arrive3(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void consumer_sync3(int nthreads) {
-    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
-}
 
 constexpr int RPT3 = 4;                                   // y rows per consumer thread
 constexpr int CONS3 = (PTZ / 2) * (PTY / RPT3);           // 512 consumer threads
@@ -229,20 +223,20 @@ diff3d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
             // plane x-1 and this Cp plane are no longer needed
             __syncwarp();
             if ((tid & 31) == 0) {
-                mbar_arrive3(&emptyT[q0 % NT]);
-                mbar_arrive3(&emptyC[qc % NC]);
+                mbar_arrive(&emptyT[q0 % NT]);
+                mbar_arrive(&emptyC[qc % NC]);
             }
         }
         // the last two T planes of the column
         __syncwarp();
         if ((tid & 31) == 0) {
-            mbar_arrive3(&emptyT[(tq + n) % NT]);
-            mbar_arrive3(&emptyT[(tq + n + 1) % NT]);
+            mbar_arrive(&emptyT[(tq + n) % NT]);
+            mbar_arrive(&emptyT[(tq + n + 1) % NT]);
         }
         tq += n + 2;
         cq += n;
         if (edge_tile) {
-            consumer_sync3(CONS3);
+            consumer_sync(CONS3);
             if (tid == 0) signal_edges_3d(p.push, p.edge_tiles, lo, hi);
         }
     }

@@ -57,12 +57,6 @@ struct T2Params {
     igg_push2d push;
 };
 
-__device__ __forceinline__ void mbar_arrive_(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void consumer_sync_(int nthreads) {
-    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
-}
 
 // ---- lean path for items whose whole box lies inside the updated region (all but the items on the array edge) ----
 // Same arithmetic and the same ring / barrier protocol as the generic path below (step1_rows / step2_rows of
@@ -204,7 +198,7 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
         }
         __syncwarp();
         if (lane0 && b > 0) mbar_arrive_u32(emptyT + tprev * 8);      // T block b-1 is done
-        consumer_sync_(consumers);                                   // mid block b complete
+        consumer_sync(consumers);                                   // mid block b complete
         // ---- step 2: output rows xb - 1 + rg*RPT + r from mid rows (rg*RPT - 2 + r) ... (rg*RPT + r)
         {
             const uint32_t m0 = mc + myB;                                      // mid row rg*RPT of block b
@@ -359,8 +353,8 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                 }
             }
             __syncwarp();
-            if ((tid & 31) == 0 && b > 0) mbar_arrive_(&emptyT[(qb + SNT - 1) % SNT]);   // T block b-1 is done
-            consumer_sync_(CONSUMERS);                                                   // mid block b complete
+            if ((tid & 31) == 0 && b > 0) mbar_arrive(&emptyT[(qb + SNT - 1) % SNT]);   // T block b-1 is done
+            consumer_sync(CONSUMERS);                                                   // mid block b complete
 
             step2_rows<SRB, RPT>(bp.prevM, bp.curM, bp.prevC, bp.curC, cp, rg, xb, it.yb, x_lo, x_hi, ny, ph2, oA, oB, wA, wB);
 #pragma unroll
@@ -386,18 +380,18 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                 }
             }
             __syncwarp();
-            if ((tid & 31) == 0 && b > 0) mbar_arrive_(&emptyC[(qc + SNC - 1) % SNC]);   // Cp block b-1 is done
+            if ((tid & 31) == 0 && b > 0) mbar_arrive(&emptyC[(qc + SNC - 1) % SNC]);   // Cp block b-1 is done
         }
         __syncwarp();
         if ((tid & 31) == 0) {
-            mbar_arrive_(&emptyT[(tq + it.nbi - 1) % SNT]);
-            mbar_arrive_(&emptyC[(cq + it.nbi - 1) % SNC]);
+            mbar_arrive(&emptyT[(tq + it.nbi - 1) % SNT]);
+            mbar_arrive(&emptyC[(cq + it.nbi - 1) % SNC]);
         }
         tq += it.nbi;
         cq += it.nbi;
         mq += it.nbi;
         if (edge_tile) {
-            consumer_sync_(CONSUMERS);   // every remote store of this item has been issued
+            consumer_sync(CONSUMERS);   // every remote store of this item has been issued
             if (tid == 0) signal_edges_2d(p.push, p.edge_tiles, e_xl, e_xh, e_yl, e_yh);
         }
     }
@@ -417,7 +411,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                 }
             if ((tid & 31) == 0)
                 for (int q = 0; q < 4; ++q) red[q][tid >> 5] = v[q];
-            consumer_sync_(CONSUMERS);
+            consumer_sync(CONSUMERS);
             if (tid < 32) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -429,7 +423,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                     }
                 }
             }
-            consumer_sync_(CONSUMERS);
+            consumer_sync(CONSUMERS);
         };
         block_fold();
         if (tid == 0) {
@@ -437,7 +431,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
             __threadfence();
             is_last = atomicAdd(&p.diag->ticket, 1u) == gridDim.x - 1;
         }
-        consumer_sync_(CONSUMERS);
+        consumer_sync(CONSUMERS);
         if (is_last) {
             __threadfence();
             for (int q = 0; q < 4; ++q) v[q] = (q & 1) ? 0.0 : -INFINITY;

@@ -97,6 +97,11 @@ def diffusion2D_perf(cfg: DiffusionConfig = None, mode: str = None, variant_name
     su = setup_2d(cfg)
     if mode is None:
         mode = "fused" if cfg.fused else "plain"
+        if (mode == "fused" and int(cfg.steps_per_pass) == 2 and cfg.kernel == "tma" and cfg.ny % 2 == 0
+                and global_grid().device_type == "cuda"):
+            from ..parallel.comm import spans_nodes
+            if not spans_nodes():
+                mode = "temporal"      # same field, half the trips through memory
     n0 = native.launch_count()
     s = make_solver(cfg, mode)
     nt, warm = int(cfg.nt), min(int(cfg.warmup), max(int(cfg.nt) - 1, 0))

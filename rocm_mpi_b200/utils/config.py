@@ -50,6 +50,9 @@ class DiffusionConfig:
     transport: Optional[str] = None              # peer | nccl | host | gloo (None = default)
     kernel: str = "tma"                          # tma | direct  (stencil kernel flavour)
     fused: bool = True                           # fuse the halo push into the stencil kernel
+    steps_per_pass: int = 2                      # perf app, fused mode: 2 = two time steps per pass over memory
+                                                 # (Diffusion2D mode "temporal"; needs the TMA kernel and an even
+                                                 # ny, else 1), 1 = one fused kernel per step
     kp_path: str = "three"                       # kp app on CUDA: three (Flux!/Residual!/Update! launches per step,
                                                  # the literal form) | persistent | resident | auto (ONE launch for
                                                  # all nt steps with the kp arithmetic; auto = resident if it fits)

@@ -253,3 +253,27 @@ def test_extract_inner_and_device_gather_single_rank(shape):
     G2 = gather_interior_device(A * 2.0)             # cached buffer, second use
     assert torch.equal(G2, want * 2.0)
     igg.finalize_global_grid(finalize_dist=False)
+
+
+def test_bench_size_kernels_against_cpu_oracle():
+    """16384 x 16384 (the size bench.py times): one step of the strip-marching kernel and one two-step pass against
+    the OpenMP C++ restatement of reference scripts/diffusion_2D_perf.jl:8-10 (csrc/cpu_oracle.cpp)."""
+    import psutil
+    if psutil.virtual_memory().available < 40 << 30:
+        pytest.skip("needs ~14 GB of host memory for the CPU oracle fields")
+    nx = ny = 16384
+    g = torch.Generator().manual_seed(11)
+    T = torch.rand(nx, ny, generator=g, dtype=torch.float64)
+    Cp = torch.rand(nx, ny, generator=g, dtype=torch.float64) + 0.5
+    ph = (1.3, 1e-3, 2.0, 3.0)
+    a = T.clone()
+    native.cpu_diffusion2d_step(a, T, Cp, *ph)
+    b = a.clone()
+    native.cpu_diffusion2d_step(b, a, Cp, *ph)
+    Td, Cpd = T.cuda(), Cp.cuda()
+    T2d = Td.clone()
+    native.diffusion2d_step(T2d, Td, Cpd, *ph, variant="tma")            # nx >= 512: the strip kernel
+    assert float((T2d.cpu() - a).abs().max()) < 1e-12
+    T2d.copy_(Td)
+    native.diffusion2d_step2(T2d, Td, Cpd, *ph)
+    assert float((T2d.cpu() - b).abs().max()) < 1e-12
