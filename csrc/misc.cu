@@ -166,10 +166,33 @@ __global__ void __launch_bounds__(RED_THREADS) reduce_max_sum_kernel(const doubl
     __shared__ double sh_max[RED_THREADS / 32], sh_sum[RED_THREADS / 32];
     __shared__ bool is_last;
     double mx = -INFINITY, sm = 0.0;
-    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
-        const double v = x[e];
-        mx = igg::max_nan(mx, v);
-        sm += v;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if ((((uintptr_t)x) & 15) == 0) {
+        // 16-byte loads, four per thread in flight (a scalar 8-byte loop reached 31 % of the DRAM bandwidth)
+        const double2* __restrict__ x2 = reinterpret_cast<const double2*>(x);
+        const size_t n2 = n >> 1;
+        for (; e + 3 * stride < n2; e += 4 * stride) {
+            const double2 a = x2[e], b = x2[e + stride], c = x2[e + 2 * stride], d = x2[e + 3 * stride];
+            mx = igg::max_nan(mx, igg::max_nan(igg::max_nan(a.x, a.y), igg::max_nan(b.x, b.y)));
+            mx = igg::max_nan(mx, igg::max_nan(igg::max_nan(c.x, c.y), igg::max_nan(d.x, d.y)));
+            sm += ((a.x + a.y) + (b.x + b.y)) + ((c.x + c.y) + (d.x + d.y));
+        }
+        for (; e < n2; e += stride) {
+            const double2 a = x2[e];
+            mx = igg::max_nan(mx, igg::max_nan(a.x, a.y));
+            sm += a.x + a.y;
+        }
+        if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+            mx = igg::max_nan(mx, x[n - 1]);
+            sm += x[n - 1];
+        }
+    } else {
+        for (; e < n; e += stride) {
+            const double v = x[e];
+            mx = igg::max_nan(mx, v);
+            sm += v;
+        }
     }
     block_reduce(mx, sm, sh_max, sh_sum);
     if (threadIdx.x == 0) {

@@ -277,3 +277,38 @@ def test_bench_size_kernels_against_cpu_oracle():
     T2d.copy_(Td)
     native.diffusion2d_step2(T2d, Td, Cpd, *ph)
     assert float((T2d.cpu() - b).abs().max()) < 1e-12
+
+
+@pytest.mark.parametrize("n,offset", [(1, 0), (2, 0), (7, 0), (1000, 1), (100003, 0), (262144 + 5, 1)])
+def test_reduce_max_sum_odd_lengths_and_unaligned_views(n, offset):
+    """The reduction reads 16-byte pairs when the input is 16-byte aligned and single values otherwise (a view that
+    starts at an odd element); odd lengths have a one-element tail."""
+    g = torch.Generator().manual_seed(n)
+    base = torch.rand(n + offset, generator=g, dtype=torch.float64).cuda()
+    x = base[offset:]
+    out = native.reduce_max_sum(x).cpu()
+    assert float(out[0]) == float(x.max())
+    assert abs(float(out[1]) - float(x.sum())) < 1e-9 * max(1.0, n)
+    y = x.clone()
+    y[n // 2] = float("nan")
+    out = native.reduce_max_sum(y).cpu()
+    assert out[0] != out[0] and out[1] != out[1]          # NaN shows up in the max as well as in the sum
+
+
+def test_in_kernel_diagnostics_report_nan():
+    """A blown-up field must show in the max, not only in the sum (the reference's maximum(T_v) propagates NaN,
+    scripts/diffusion_2D_perf_hide.jl:115): one-step kernels (tile and strip) and the two-step kernel."""
+    for shape in [(300, 380), (1100, 512)]:
+        T = torch.rand(*shape, dtype=torch.float64, device="cuda")
+        T[shape[0] // 2, shape[1] // 2] = float("nan")
+        Cp = torch.ones_like(T)
+        T2 = T.clone()
+        d = torch.zeros(2, dtype=torch.float64, device="cuda")
+        native.diffusion2d_step(T2, T, Cp, 1.0, 1e-4, 2.0, 3.0, variant="tma", diag_out=d)
+        v = d.cpu()
+        assert v[0] != v[0] and v[1] != v[1], (shape, v)
+        d4 = torch.zeros(4, dtype=torch.float64, device="cuda")
+        T2.copy_(T)
+        native.diffusion2d_step2(T2, T, Cp, 1.0, 1e-4, 2.0, 3.0, diag_out=d4)
+        v = d4.cpu()
+        assert all(bool(x != x) for x in v), (shape, v)
