@@ -4,8 +4,8 @@
 Generalises the reference's 32-byte smoke test (``scripts/rocmaware_test_selectdevice.jl:15-22``) into a
 measurement: every rank sends ``bytes`` to its ring successor and receives from its predecessor,
 
-* ``peer``  -- one peer-store kernel (16-byte stores through a peer-mapped pointer) + release flag; the
-               receiver's stream waits on the flag (what the halo fabric does);
+* ``peer``  -- ONE kernel: 16-byte stores through a peer-mapped pointer, release flag into the receiver's memory,
+               wait for the own flag (``igg_peer_sendrecv``: what the halo fabric does);
 * ``nccl``  -- grouped NCCL ``isend``/``irecv`` (the baseline).
 
 Time is measured on the device (CUDA events around ``iters`` back-to-back exchanges, max over ranks) and
@@ -62,9 +62,8 @@ def main() -> int:
                 nonlocal epoch
                 if tr == "peer":
                     epoch += 1
-                    native._check(lib.igg_peer_copy(dst_ptr, send.data_ptr(), size, flag_ptr, epoch, cnt.data_ptr(),
-                                                    native._stream()))
-                    native._check(lib.igg_wait_value(flag.data_ptr(), epoch, flag[1:].data_ptr(), native._stream()))
+                    native._check(lib.igg_peer_sendrecv(dst_ptr, send.data_ptr(), size, flag_ptr, flag.data_ptr(), epoch,
+                                                        cnt.data_ptr(), flag[1:].data_ptr(), native._stream()))
                 elif nprocs > 1:
                     g.comm.exchange([(send[: size // 8], dst, 0)], [(recv_n[: size // 8], src, 0)])
                 else:

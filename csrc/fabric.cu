@@ -243,7 +243,8 @@ constexpr int PC_THREADS = 512;
 __global__ void __launch_bounds__(PC_THREADS) peer_copy_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src,
                                                                size_t n16, unsigned char* dst_tail,
                                                                const unsigned char* src_tail, int tail,
-                                                               uint64_t* peer_flag, uint64_t value, uint64_t* my_count) {
+                                                               uint64_t* peer_flag, uint64_t value, uint64_t* my_count,
+                                                               const uint64_t* my_flag, uint64_t* err_word) {
     const size_t stride = (size_t)gridDim.x * PC_THREADS;
     size_t e = (size_t)blockIdx.x * PC_THREADS + threadIdx.x;
     // 4 independent 16-byte loads in flight per thread
@@ -267,6 +268,8 @@ __global__ void __launch_bounds__(PC_THREADS) peer_copy_kernel(uint4* __restrict
             }
         }
     }
+    // send + receive in ONE launch: the launch is complete when the matching message has landed here too
+    if (my_flag && blockIdx.x == 0 && threadIdx.x == 0) wait_flag_ge(my_flag, value, err_word);
 }
 
 }  // namespace
@@ -390,7 +393,24 @@ int igg_peer_copy(void* dst, const void* src, size_t bytes, uint64_t* peer_flag,
     if (blocks < 1) blocks = 1;
     peer_copy_kernel<<<(int)blocks, PC_THREADS, 0, (cudaStream_t)stream>>>(
         (uint4*)dst, (const uint4*)src, n16, (unsigned char*)dst + n16 * 16, (const unsigned char*)src + n16 * 16, tail,
-        peer_flag, flag_value, my_count);
+        peer_flag, flag_value, my_count, nullptr, nullptr);
+    IGG_LAUNCH_CHECK();
+    return 0;
+}
+
+int igg_peer_sendrecv(void* dst, const void* src, size_t bytes, uint64_t* peer_flag, const uint64_t* my_flag,
+                      uint64_t flag_value, uint64_t* my_count, uint64_t* err_word, void* stream) {
+    IGG_REQUIRE(dst && src && bytes > 0 && peer_flag && my_flag && my_count, "igg_peer_sendrecv: bad arguments");
+    IGG_REQUIRE((((uintptr_t)dst | (uintptr_t)src) & 15) == 0, "igg_peer_sendrecv: pointers must be 16-byte aligned");
+    const size_t n16 = bytes / 16;
+    const int tail = (int)(bytes % 16);
+    size_t blocks = (n16 + (size_t)PC_THREADS * 4 - 1) / ((size_t)PC_THREADS * 4);
+    const size_t cap = (size_t)igg::sm_count() * 2;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    peer_copy_kernel<<<(int)blocks, PC_THREADS, 0, (cudaStream_t)stream>>>(
+        (uint4*)dst, (const uint4*)src, n16, (unsigned char*)dst + n16 * 16, (const unsigned char*)src + n16 * 16, tail,
+        peer_flag, flag_value, my_count, my_flag, err_word);
     IGG_LAUNCH_CHECK();
     return 0;
 }

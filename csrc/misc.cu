@@ -60,46 +60,49 @@ __global__ void unpack_plane_kernel(double* __restrict__ A, int n0, int n1, int 
 // unit: two 8-byte loads (the interior starts one element into the row, so the source is only 8-byte aligned) and one
 // 16-byte store when the destination is 16-byte aligned -- the width NVLink stores want -- else two 8-byte stores.
 constexpr int CIR_THREADS = 256;
+constexpr int CIR_SEG_UNITS = 4 * CIR_THREADS;        // one work item = 1024 two-element units (16 KB) of one row
 __global__ void __launch_bounds__(CIR_THREADS) copy_inner_rows_kernel(const double* __restrict__ A, int n1, int n2,
                                                                       int m1, int m2, int o0, int o1, int o2,
                                                                       double* __restrict__ G, long long G1, long long G2,
                                                                       long long g0, long long g1, long long g2,
                                                                       long long rows) {
+    // Work items are (row, segment) pairs with the segment running fastest, handed to the CTAs round-robin: at any
+    // moment the grid works on a window of neighbouring 16 KB segments, like a plain copy does (one whole row per
+    // CTA scattered 1184 concurrent streams over 100 MB and reached 54 % of the copy bandwidth).
     const int upr = m2 >> 1;                          // two-element units per row (+ one tail element if m2 is odd)
-    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int segs = upr > 0 ? (upr + CIR_SEG_UNITS - 1) / CIR_SEG_UNITS : 1;
+    const long long items = rows * segs;
+    for (long long item = blockIdx.x; item < items; item += gridDim.x) {
+        const long long row = item / segs;
+        const int seg = (int)(item - row * segs);
         const long long a = row / m1, b = row - a * m1;
         const double* __restrict__ src = A + ((a + o0) * (long long)n1 + (b + o1)) * (long long)n2 + o2;
         double* __restrict__ dst = G + ((a + g0) * G1 + (b + g1)) * G2 + g2;
         const bool al16 = (((uintptr_t)dst) & 15) == 0;
-        int u = threadIdx.x;
-        for (; u + 3 * CIR_THREADS < upr; u += 4 * CIR_THREADS) {      // four units in flight per thread
-            double x[4], y[4];
+        const int u0 = seg * CIR_SEG_UNITS + threadIdx.x;
+        double x[4], y[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                x[q] = src[2 * (u + q * CIR_THREADS)];
-                y[q] = src[2 * (u + q * CIR_THREADS) + 1];
+        for (int q = 0; q < 4; ++q) {                 // four units in flight per thread
+            const int u = u0 + q * CIR_THREADS;
+            if (u < upr) {
+                x[q] = __ldcs(src + 2 * u);
+                y[q] = __ldcs(src + 2 * u + 1);
             }
+        }
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                double* d = dst + 2 * (u + q * CIR_THREADS);
+        for (int q = 0; q < 4; ++q) {
+            const int u = u0 + q * CIR_THREADS;
+            if (u < upr) {
+                double* d = dst + 2 * u;
                 if (al16) {
-                    *reinterpret_cast<double2*>(d) = make_double2(x[q], y[q]);
+                    __stcs(reinterpret_cast<double2*>(d), make_double2(x[q], y[q]));
                 } else {
-                    d[0] = x[q];
-                    d[1] = y[q];
+                    __stcs(d, x[q]);
+                    __stcs(d + 1, y[q]);
                 }
             }
         }
-        for (; u < upr; u += CIR_THREADS) {
-            const double x = src[2 * u], y = src[2 * u + 1];
-            if (al16) {
-                *reinterpret_cast<double2*>(dst + 2 * u) = make_double2(x, y);
-            } else {
-                dst[2 * u] = x;
-                dst[2 * u + 1] = y;
-            }
-        }
-        if ((m2 & 1) && threadIdx.x == 0) dst[m2 - 1] = src[m2 - 1];
+        if ((m2 & 1) && seg == segs - 1 && threadIdx.x == 0) dst[m2 - 1] = src[m2 - 1];
     }
 }
 
@@ -117,7 +120,8 @@ static int launch_copy_inner(const double* A, int n0, int n1, int n2, double* G,
     const int o0 = n0 > 2, o1 = n1 > 2, o2 = n2 > 2;
     const int m0 = n0 - 2 * o0, m1 = n1 - 2 * o1, m2 = n2 - 2 * o2;
     const long long rows = (long long)m0 * m1;
-    long long grid = rows;
+    const int upr = m2 >> 1;
+    long long grid = rows * (upr > 0 ? (upr + CIR_SEG_UNITS - 1) / CIR_SEG_UNITS : 1);
     const long long cap = (long long)igg::sm_count() * 8;
     if (grid > cap) grid = cap;
     if (grid < 1) grid = 1;

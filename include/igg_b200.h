@@ -313,6 +313,11 @@ int igg_wait_epoch(const igg_halo_sync* sync, void* stream);
  * *peer_flag = flag_value (release, system scope).  `my_count` is a private zero-initialised counter. */
 int igg_peer_copy(void* dst, const void* src, size_t bytes, uint64_t* peer_flag, uint64_t flag_value,
                   uint64_t* my_count, void* stream);
+/* The device-buffer Sendrecv of reference scripts/rocmaware_test_selectdevice.jl:22 as ONE launch: store `src` into the
+ * peer's `dst`, release `flag_value` to `peer_flag` (in the receiver's memory), and do not finish before `my_flag` (in
+ * mine, released by whoever sends to me) has reached `flag_value` too. */
+int igg_peer_sendrecv(void* dst, const void* src, size_t bytes, uint64_t* peer_flag, const uint64_t* my_flag,
+                      uint64_t flag_value, uint64_t* my_count, uint64_t* err_word, void* stream);
 /* wait until *my_flag >= value */
 int igg_wait_value(uint64_t* my_flag, uint64_t value, uint64_t* err_word, void* stream);
 

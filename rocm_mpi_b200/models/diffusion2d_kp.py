@@ -128,8 +128,9 @@ def diffusion2D_kp(cfg: DiffusionConfig = None, finalize: bool = True) -> RunRes
         raise ValueError("kp_path must be three | persistent | resident | auto")
     if on_gpu and cfg.kp_path != "three":
         return _single_launch(cfg, s, finalize)
-    n0 = native.launch_count()
-    kp = KPThree(cfg.nx, cfg.ny, s.dx, s.dy, s.dt, cfg.lam, cfg.Cp0, initial_condition_2d(s), transport, cfg.fused)
+    T0 = initial_condition_2d(s)
+    n0 = native.launch_count()            # launches of the time loop (the reference's 3 per step), not of the set-up
+    kp = KPThree(cfg.nx, cfg.ny, s.dx, s.dy, s.dt, cfg.lam, cfg.Cp0, T0, transport, cfg.fused)
     log0("Starting the time loop ...", end="")
     kp.step(int(cfg.nt))
     kp.finish()

@@ -61,9 +61,9 @@ def selectdevice_test(N: int = 4, transports=("peer", "nccl"), quiet: bool = Fal
                 dst_ptr, flag_ptr = fab.peer_ptr(recv, dst), fab.peer_ptr(flag, dst)
             else:
                 dst_ptr, flag_ptr = recv.data_ptr(), flag.data_ptr()
-            native._check(lib.igg_peer_copy(dst_ptr, send.data_ptr(), N * 8, flag_ptr, 1, cnt.data_ptr(),
-                                            native._stream()))
-            native._check(lib.igg_wait_value(flag.data_ptr(), 1, flag[1:].data_ptr(), native._stream()))
+            # send + receive in ONE launch: store into the successor's buffer, release its flag, wait for mine
+            native._check(lib.igg_peer_sendrecv(dst_ptr, send.data_ptr(), N * 8, flag_ptr, flag.data_ptr(), 1,
+                                                cnt.data_ptr(), flag[1:].data_ptr(), native._stream()))
             torch.cuda.synchronize()
             if int(flag[1]) != 0:
                 raise RuntimeError("peer flag wait timed out")

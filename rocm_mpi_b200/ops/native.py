@@ -104,6 +104,7 @@ def _declare(lib) -> None:
         "igg_ipc_close": ([vp], i),
         "igg_can_access_peer": ([i, i, C.POINTER(i)], i),
         "igg_gather_inner": ([vp, i, i, i, vp, i, i, i, i, i, i, vp], i),
+        "igg_peer_sendrecv": ([vp, vp, sz, vp, vp, u64, vp, vp, vp], i),
         "igg_halo_exchange_peer": ([vp, i, C.POINTER(HaloSync), vp], i),
         "igg_halo_exchange_peer_ex": ([vp, i, C.POINTER(HaloSync), i, vp], i),
         "igg_neighbor_barrier": ([C.POINTER(HaloSync), vp], i),
