@@ -332,8 +332,8 @@ class Diffusion2D:
         flight.  Every step still moves 32 B in and 16 B out, but the device never idles waiting for the host --
         the reference's loop does not block the device per step either (``scripts/diffusion_2D_perf.jl:47-52``)."""
         if pipelined:
-            if not (self.mode == "fused" and self.variant == "tma"):
-                raise ValueError("pipelined control needs mode='fused', variant='tma' (or step_controlled_pair)")
+            if not (self.mode in ("fused", "temporal") and self.variant == "tma"):
+                raise ValueError("pipelined control needs mode='fused' or 'temporal' with variant='tma'")
             return self._step_controlled_pipelined(lam, dt, pair=False)
         if self._ctl_pending:
             raise RuntimeError("pipelined steps are in flight: call drain_controlled() first")
@@ -342,9 +342,9 @@ class Diffusion2D:
         p[1] = self.dt if dt is None else dt
         p[2] = self._dx
         p[3] = self._dy
-        if self.mode == "fused" and self.variant == "tma":
+        if self.mode in ("fused", "temporal") and self.variant == "tma":
             # the whole step -- H2D 32 B, fused kernel with in-kernel diagnostic, D2H 16 B, sync -- is one
-            # native call
+            # native call (in mode 'temporal' this is the single step that completes an odd count)
             if not self._running:
                 self.begin()
             native.diffusion2d_step_controlled(self.T2, self.T, self.Cp, p, self._params_dev, self._diag_dev,

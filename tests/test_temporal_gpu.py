@@ -99,3 +99,33 @@ def test_controlled_pairs_match_controlled_steps():
     for g, w in zip(got, want):
         assert abs(g[0] - w[0]) < TOL and abs(g[1] - w[1]) < 1e-9 * 130 * 258
     igg.finalize_global_grid(finalize_dist=False)
+
+
+def test_pipelined_pairs_with_an_odd_tail_match_blocking_steps():
+    """Pipelined control loop in mode 'temporal': pairs, then ONE single step (an odd step count), every diagnostic
+    seen exactly once and equal to the blocking one-step loop's."""
+    from rocm_mpi_b200.models.solver import Diffusion2D
+    igg.init_global_grid(130, 258, 1, periodx=1, periody=1, quiet=True, init_dist=False)
+    s = Diffusion2D(130, 258, mode="fused")
+    want = [s.step_controlled() for _ in range(7)]
+    s.finish()
+    Tf = s.T.clone()
+    igg.finalize_global_grid(finalize_dist=False)
+    igg.init_global_grid(130, 258, 1, periodx=1, periody=1, quiet=True, init_dist=False)
+    s = Diffusion2D(130, 258, mode="temporal")
+    got = []
+    for _ in range(3):
+        r = s.step_controlled_pair(pipelined=True)
+        if r is not None:
+            got += list(r)
+    r = s.step_controlled(pipelined=True)
+    if r is not None:
+        got += list(r) if isinstance(r[0], tuple) else [r]
+    for r in s.drain_controlled():
+        got += list(r) if isinstance(r[0], tuple) else [r]
+    s.finish()
+    assert len(got) == 7
+    assert float((s.T - Tf).abs().max()) < TOL
+    for g_, w in zip(got, want):
+        assert abs(g_[0] - w[0]) < TOL and abs(g_[1] - w[1]) < 1e-9 * 130 * 258
+    igg.finalize_global_grid(finalize_dist=False)
