@@ -218,6 +218,10 @@ __device__ __forceinline__ double update_cell_kp(double c, double xm, double xp,
     return c + dt * dTdt;
 }
 
+// max for the hot loops of the in-kernel diagnostics: one compare + select (fmax() expands to a NaN-aware sequence
+// of ~5 instructions on sm_100a).  It drops NaNs like fmax; the kernels restore them from the sum at the final fold.
+__device__ __forceinline__ double max_fast(double a, double b) { return a > b ? a : b; }
+
 // streaming (evict-first) 16-byte / 8-byte global stores and read-only loads
 __device__ __forceinline__ void st_cs_f64x2(double* p, double a, double b) {
     asm volatile("st.global.cs.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");

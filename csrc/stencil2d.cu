@@ -135,7 +135,7 @@ __device__ __forceinline__ void diag_finish(DiagScratch* scratch, double* diag_o
     auto block_fold = [&](double& mx, double& sm) {
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) {
-            mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+            mx = igg::max_fast(mx, __shfl_xor_sync(0xffffffffu, mx, off));
             sm += __shfl_xor_sync(0xffffffffu, sm, off);
         }
         if ((tid & 31) == 0) { red[tid >> 5] = mx; red[32 + (tid >> 5)] = sm; }
@@ -145,7 +145,7 @@ __device__ __forceinline__ void diag_finish(DiagScratch* scratch, double* diag_o
             sm = tid < NCW ? red[32 + tid] : 0.0;
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) {
-                mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+                mx = igg::max_fast(mx, __shfl_xor_sync(0xffffffffu, mx, off));
                 sm += __shfl_xor_sync(0xffffffffu, sm, off);
             }
         }
@@ -164,7 +164,7 @@ __device__ __forceinline__ void diag_finish(DiagScratch* scratch, double* diag_o
         dmax = -INFINITY;
         dsum = 0.0;
         for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS) {
-            dmax = fmax(dmax, scratch->pmax[b2]);
+            dmax = igg::max_fast(dmax, scratch->pmax[b2]);
             dsum += scratch->psum[b2];
         }
         block_fold(dmax, dsum);
@@ -287,8 +287,8 @@ diff2d_tma_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constan
                 if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
             }
             if (diag) {
-                if (wA) { dmax = fmax(dmax, vA); dsum += vA; }
-                if (wB) { dmax = fmax(dmax, vB); dsum += vB; }
+                if (wA) { dmax = igg::max_fast(dmax, vA); dsum += vA; }
+                if (wB) { dmax = igg::max_fast(dmax, vB); dsum += vB; }
             }
             a = b;
             b = c;
@@ -468,8 +468,8 @@ diff2d_strip_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_const
                     if (wB) push_cell_2d(p.push, p.nx, p.ny, x, y + 1, vB);
                 }
                 if (diag) {
-                    if (wA) { dmax = fmax(dmax, vA); dsum += vA; }
-                    if (wB) { dmax = fmax(dmax, vB); dsum += vB; }
+                    if (wA) { dmax = igg::max_fast(dmax, vA); dsum += vA; }
+                    if (wB) { dmax = igg::max_fast(dmax, vB); dsum += vB; }
                 }
                 a = bb;
                 bb = c;

@@ -113,7 +113,7 @@ __device__ __forceinline__ void t2_lean_step1(uint32_t pa, uint32_t pb, uint32_t
         sts128(pm + r * ROWB, mA, mB);
         if (DIAG) {
             if (!EDGE || (xr0 + r >= x_lo && xr0 + r <= x_hi)) {
-                imax = fmax(imax, fmax(mA, mB));
+                imax = igg::max_fast(imax, igg::max_fast(mA, mB));
                 isum += mA + mB;
             }
         }
@@ -143,7 +143,7 @@ __device__ __forceinline__ void t2_lean_step2(uint32_t mm2, uint32_t mm1, uint32
         if (pair_ok && row_ok) st_cs_f64x2(out + (size_t)r * ny, oA, oB);
         if (DIAG) {
             if (row_ok) {
-                imax = fmax(imax, fmax(oA, oB));
+                imax = igg::max_fast(imax, igg::max_fast(oA, oB));
                 isum += oA + oB;
             }
         }
@@ -225,9 +225,9 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
         mbar_arrive_u32(emptyC + cprev * 8);
     }
     if (DIAG && pair_ok) {
-        acc.d1max = fmax(acc.d1max, i1max);
+        acc.d1max = igg::max_fast(acc.d1max, i1max);
         acc.d1sum += i1sum;
-        acc.d2max = fmax(acc.d2max, i2max);
+        acc.d2max = igg::max_fast(acc.d2max, i2max);
         acc.d2sum += i2sum;
     }
 }
@@ -348,8 +348,8 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                 step1_own_masks<RPT>(cp, rg, xb, it.yb, x_lo, x_hi, ny, wA, wB);
 #pragma unroll
                 for (int r = 0; r < RPT; ++r) {
-                    if ((wA >> r) & 1u) { d1max = fmax(d1max, oA[r]); d1sum += oA[r]; }
-                    if ((wB >> r) & 1u) { d1max = fmax(d1max, oB[r]); d1sum += oB[r]; }
+                    if ((wA >> r) & 1u) { d1max = igg::max_fast(d1max, oA[r]); d1sum += oA[r]; }
+                    if ((wB >> r) & 1u) { d1max = igg::max_fast(d1max, oB[r]); d1sum += oB[r]; }
                 }
             }
             __syncwarp();
@@ -374,8 +374,8 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
                         if (c) push_cell_2d(p.push, nx, ny, x, y + 1, oB[r]);
                     }
                     if (diag) {
-                        if (a) { d2max = fmax(d2max, oA[r]); d2sum += oA[r]; }
-                        if (c) { d2max = fmax(d2max, oB[r]); d2sum += oB[r]; }
+                        if (a) { d2max = igg::max_fast(d2max, oA[r]); d2sum += oA[r]; }
+                        if (c) { d2max = igg::max_fast(d2max, oB[r]); d2sum += oB[r]; }
                     }
                 }
             }

@@ -19,7 +19,7 @@ echo "== bench ours (two-step) N=$N"
 timeout 400 $TR bench.py --gpus $N --steps 50 --warmup 10 > $OUT/m${N}_bench_ours.json 2> $OUT/m${N}_bench_ours.err; echo "rc=$?"; cut -c1-330 $OUT/m${N}_bench_ours.json; grep -v "OMP_NUM\|\*\*\*\*" $OUT/m${N}_bench_ours.err | tail -n 3
 echo "== bench fused (one step per pass) N=$N"
 timeout 400 $TR bench.py --gpus $N --steps 50 --warmup 10 --kernel fused --no-baseline > $OUT/m${N}_bench_fused.json 2> $OUT/m${N}_bench_fused.err; echo "rc=$?"; cut -c1-330 $OUT/m${N}_bench_fused.json
-echo "== bench hide (frame || interior on two priority streams, b_width 16 4) N=$N"
+[ -z "$QUICK" ] && echo "== bench hide (frame || interior on two priority streams, b_width 16 4) N=$N" && \
 timeout 400 $TR bench.py --gpus $N --steps 50 --warmup 10 --impl hide --no-baseline > $OUT/m${N}_bench_hide.json 2> $OUT/m${N}_bench_hide.err; echo "rc=$?"; cut -c1-330 $OUT/m${N}_bench_hide.json
 echo "== update_halo API sweep N=$N"
 timeout 400 $TR benchmarks/update_halo_sweep.py --out $OUT/m${N}_update_halo_sweep.json 2>&1 | grep "^{" | tail -n 8
@@ -31,7 +31,7 @@ timeout 300 $TR benchmarks/small_grid_latency.py $L --out $OUT/m${N}_small_254.j
 echo "== small-grid latency, literal 252 x 252 local N=$N"
 timeout 300 $TR benchmarks/small_grid_latency.py --nx 252 --ny 252 --out $OUT/m${N}_small_252.json 2>&1 | grep "^{" | tail -n 1
 echo "== gather bench N=$N"
-timeout 300 $TR benchmarks/gather_bench.py --n 12288 --out $OUT/m${N}_gather.json 2>&1 | grep "^{" | tail -n 1
+timeout 300 $TR benchmarks/gather_bench.py --n 12288 --out $OUT/m${N}_gather.json > $OUT/m${N}_gather.log 2>&1; echo "rc=$?"; grep "^{" $OUT/m${N}_gather.log | tail -n 1; grep -E "Error|error|Traceback" -A3 $OUT/m${N}_gather.log | grep -v Warning | tail -n 12
 if [ "$N" = "8" ]; then
   echo "== 3-D weak scaling 512^3 per GPU on 2x2x2"
   timeout 300 $TR -m rocm_mpi_b200.models.diffusion3d --nx 512 --ny 512 --nz 512 --nt 60 --warmup 10 --dimx 2 --dimy 2 --dimz 2 --do-vis 0 --quiet 0 2>&1 | grep -E "Executed|Global grid" | tail -n 2 | tee $OUT/m${N}_3d_512.txt
