@@ -466,7 +466,15 @@ struct MidParams {
     uint64_t epoch;
 };
 
-constexpr int MID_CTAS_PER_FACE = 8;
+// CTAs per face: one per 512 cells of the longer edge, at most 32 (a line is pure latency -- six dependent-free loads,
+// one remote store per cell -- so it is spread wide; the arrival counter is taken modulo this number, which depends
+// only on the field shape and is therefore the same for every launch of a time loop)
+constexpr int MID_MAX_CTAS_PER_FACE = 32;
+static int mid_ctas_per_face(int nx, int ny) {
+    const int n = nx > ny ? nx : ny;
+    int c = (n + 511) / 512;
+    return c < 1 ? 1 : (c > MID_MAX_CTAS_PER_FACE ? MID_MAX_CTAS_PER_FACE : c);
+}
 
 __global__ void __launch_bounds__(256) diff2d_midlines_kernel(const __grid_constant__ MidParams p) {
     const int face = blockIdx.y;
@@ -645,7 +653,7 @@ extern "C" int igg_diffusion2d_midlines(const double* T, const double* Cp, int n
     p.err_word = push->err_word;
     p.epoch = push->epoch;
     if (!any) return 0;
-    dim3 grid(MID_CTAS_PER_FACE, 4);
+    dim3 grid(mid_ctas_per_face(nx, ny), 4);
     diff2d_midlines_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
     IGG_LAUNCH_CHECK();
     return 0;
