@@ -122,9 +122,14 @@ class NvlinkCounters:
             pynvml.nvmlInit()
             self.nv = pynvml
             self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
-            self.ids = [(pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
-                        (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF)]
-            if self.read() is None:
+            tx, rx = pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX
+            # the all-links scope first; some drivers only answer per link
+            for ids in ([(tx, 0xFFFFFFFF), (rx, 0xFFFFFFFF)],
+                        [(tx, k) for k in range(18)] + [(rx, k) for k in range(18)]):
+                self.ids = ids
+                if self.read() is not None:
+                    break
+            else:
                 self.h = None
         except Exception:
             self.h = None
@@ -134,11 +139,12 @@ class NvlinkCounters:
             return None
         try:
             v = self.nv.nvmlDeviceGetFieldValues(self.h, self.ids)
-            out = []
-            for x in v:
+            half = len(v) // 2
+            out = [0, 0]
+            for k, x in enumerate(v):
                 if x.nvmlReturn != 0:
                     return None
-                out.append(int(x.value.ullVal) * 1024)
+                out[0 if k < half else 1] += int(x.value.ullVal) * 1024
             return out
         except Exception:
             return None
