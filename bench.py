@@ -433,6 +433,8 @@ def main() -> int:
     if ver is not None and not ver["ok"]:
         rc = 3
     g.comm.finalize()
+    if torch.distributed.is_available() and torch.distributed.is_initialized():
+        torch.distributed.destroy_process_group()       # explicit: no "was not called before program exit" warning
     return rc
 
 

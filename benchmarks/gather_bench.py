@@ -10,7 +10,7 @@ over MPI, ``heatmap`` on rank 0.  Here:
 * ``host``    -- the reference's structure (device -> pinned host on every rank, gloo gather), once, for comparison;
 * ``heatmap`` -- colour map of the gathered field on the root GPU + PNG encoding.
 
-Run:  ``torchrun --nproc-per-node 8 benchmarks/gather_bench.py --n 12288 [--out file.json]``
+Run:  ``torchrun --nproc-per-node 8 benchmarks/gather_bench.py --size 12288 [--out file.json]``
 """
 from __future__ import annotations
 
@@ -31,9 +31,9 @@ from rocm_mpi_b200.utils.output import save_heatmap  # noqa: E402
 
 def main() -> int:
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=12288)
+    ap.add_argument("--size", dest="n", type=int, default=12288, help="local grid is size x size")
     ap.add_argument("--reps", type=int, default=5)
-    ap.add_argument("--host-n", type=int, default=4096, help="local size of the host-staged comparison (0 = skip)")
+    ap.add_argument("--host-size", dest="host_n", type=int, default=4096, help="local size of the host-staged comparison (0 = skip)")
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
     res = {"bench": "gather", "local": [a.n, a.n]}
@@ -63,10 +63,8 @@ def main() -> int:
         # every tile where it belongs: f(global index) is smooth, so compare against the closed form
         X = torch.arange(G.shape[0], device=dev, dtype=torch.float64)
         Y = torch.arange(G.shape[1], device=dev, dtype=torch.float64)
-        bx = torch.div(X, a.n - 2, rounding_mode="floor")
-        by = torch.div(Y, a.n - 2, rounding_mode="floor")
-        gxx = X + 1 + 0 * bx                               # global index of gathered row r is r + 1
-        gyy = Y + 1 + 0 * by
+        gxx = X + 1                                        # global index of gathered row r is r + 1
+        gyy = Y + 1
         want = torch.exp(-((gxx[:, None] / (dims[0] * a.n) - 0.5) ** 2) - (gyy[None, :] / (dims[1] * a.n) - 0.5) ** 2)
         ok = bool(torch.equal(G, want))
         del want

@@ -31,7 +31,7 @@ timeout 300 $TR benchmarks/small_grid_latency.py $L --out $OUT/m${N}_small_254.j
 echo "== small-grid latency, literal 252 x 252 local N=$N"
 timeout 300 $TR benchmarks/small_grid_latency.py --nx 252 --ny 252 --out $OUT/m${N}_small_252.json 2>&1 | grep "^{" | tail -n 1
 echo "== gather bench N=$N"
-timeout 300 $TR benchmarks/gather_bench.py --n 12288 --out $OUT/m${N}_gather.json > $OUT/m${N}_gather.log 2>&1; echo "rc=$?"; grep "^{" $OUT/m${N}_gather.log | tail -n 1; grep -E "Error|error|Traceback" -A3 $OUT/m${N}_gather.log | grep -v Warning | tail -n 12
+timeout 300 $TR benchmarks/gather_bench.py --size 12288 --out $OUT/m${N}_gather.json > $OUT/m${N}_gather.log 2>&1; echo "rc=$?"; grep "^{" $OUT/m${N}_gather.log | tail -n 1; grep -E "Error|error|Traceback" -A3 $OUT/m${N}_gather.log | grep -v Warning | tail -n 12
 if [ "$N" = "8" ]; then
   echo "== 3-D weak scaling 512^3 per GPU on 2x2x2"
   timeout 300 $TR -m rocm_mpi_b200.models.diffusion3d --nx 512 --ny 512 --nz 512 --nt 60 --warmup 10 --dimx 2 --dimy 2 --dimz 2 --do-vis 0 --quiet 0 2>&1 | grep -E "Executed|Global grid" | tail -n 2 | tee $OUT/m${N}_3d_512.txt
