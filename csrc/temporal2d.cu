@@ -529,7 +529,12 @@ static int launch_t2d(const CUtensorMap& mT, const CUtensorMap& mC, const T2Para
         igg::set_error("igg_diffusion2d_step2: more than 1024 CTAs (%d) do not fit the diagnostic scratch", grid);
         return IGG_ERR_UNSUPPORTED;
     }
-    kern<<<grid, NPAIR*(SRB / RPT) + 32, T2_SMEM_BYTES, st>>>(mT, mC, p);
+    // one interior item per CTA before the edge items (IGG_T2_LEAD=0: edge items first)
+    static int lead_on = -1;
+    if (lead_on < 0) lead_on = env_int_("IGG_T2_LEAD", 1);
+    T2Params q = p;
+    set_lead(q.g, lead_on ? grid : 0);
+    kern<<<grid, NPAIR*(SRB / RPT) + 32, T2_SMEM_BYTES, st>>>(mT, mC, q);
     return 0;
 }
 

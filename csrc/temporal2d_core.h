@@ -113,7 +113,10 @@ struct Geom {
     int srb;        // rows per block (8 or 16)
     int scx;        // output rows per strip, (scx + 4) % srb == 0
     int nti, ntj;   // strips, tile columns
-    int frame_first;  // 1: items on the array edge come first (they push to the neighbours)
+    int frame_first;  // 1: items on the array edge come early (they push to the neighbours)
+    int lead;         // with frame_first: this many interior items are handed out BEFORE the edge items (one per
+                      // CTA), so that an edge item's wait for the neighbours' mid lines is hidden behind an item
+                      // that needs nothing from anybody; 0 = edge items first
 };
 
 inline Geom make_geom(int nx, int ny, int srb, int scx, int frame_first) {
@@ -125,16 +128,38 @@ inline Geom make_geom(int nx, int ny, int srb, int scx, int frame_first) {
     g.nti = (nx - 2 + scx - 1) / scx;
     g.ntj = (ny - 2) / BYO + 1;
     g.frame_first = frame_first;
+    g.lead = 0;
     return g;
 }
 
 T2_HD int num_items(const Geom& g) { return g.nti * g.ntj; }
 
-// item id -> (ci, j).  frame_first order: strip 0, last strip, tile column 0, last tile column, the rest.
+// item id -> (ci, j).  frame_first order: [`lead` interior items,] strip 0, last strip, tile column 0, last tile
+// column, the (remaining) interior items.  `lead` must not exceed the number of interior items (set_lead clamps).
+T2_HD void set_lead(Geom& g, int want) {
+    const int n_int = (g.nti >= 3 && g.ntj >= 3) ? (g.nti - 2) * (g.ntj - 2) : 0;
+    g.lead = (g.frame_first && want > 0) ? (want < n_int ? want : n_int) : 0;
+}
+
 T2_HD void item_of(const Geom& g, int t, int& ci, int& j) {
     if (!g.frame_first || g.nti < 3 || g.ntj < 3) {
         ci = t / g.ntj;
         j = t - ci * g.ntj;
+        return;
+    }
+    const int w0 = g.ntj - 2;
+    if (t < g.lead) {                      // leading interior items
+        ci = 1 + t / w0;
+        j = 1 + (t - (ci - 1) * w0);
+        return;
+    }
+    const int nframe = 2 * g.ntj + 2 * (g.nti - 2);
+    const int lead = g.lead;
+    t -= lead;
+    if (t >= nframe) {                     // the remaining interior items
+        t = t - nframe + lead;
+        ci = 1 + t / w0;
+        j = 1 + (t - (ci - 1) * w0);
         return;
     }
     if (t < g.ntj) { ci = 0; j = t; return; }

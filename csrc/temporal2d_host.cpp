@@ -120,7 +120,8 @@ extern "C" int igg_cpu_temporal2d_emulate(const double* T, double* T2, const dou
     if (scx < srb - 4 || scx < 4 || (scx + 4) % srb || workers < 1 || (rpt != 2 && rpt != 4)) return IGG_ERR_INVALID;
     if (srb == 4 && rpt != 2) return IGG_ERR_INVALID;
     if (side_mask && !mid_lines) return IGG_ERR_INVALID;
-    const Geom g = make_geom(nx, ny, srb, scx, side_mask ? 1 : 0);
+    Geom g = make_geom(nx, ny, srb, scx, side_mask ? 1 : 0);
+    set_lead(g, workers);                  // as the kernel launch does: one interior item per worker first
     Phys ph;
     ph.lam = lam;
     ph.dt = dt;
