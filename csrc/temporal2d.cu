@@ -233,7 +233,10 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
 }
 
 template <int SRB, int RPT, bool DIAG>
-__global__ void __launch_bounds__(NPAIR*(SRB / RPT) + 32, SRB == 4 ? 4 : (SRB == 8 ? 2 : 1))
+#ifndef IGG_T2_CTAS_SRB4
+#define IGG_T2_CTAS_SRB4 4      // resident CTAs per SM with 4-row blocks (40 KB of shared memory, 160 threads each)
+#endif
+__global__ void __launch_bounds__(NPAIR*(SRB / RPT) + 32, SRB == 4 ? IGG_T2_CTAS_SRB4 : (SRB == 8 ? 2 : 1))
 diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapC,
                         const __grid_constant__ T2Params p) {
     constexpr int CONSUMERS = NPAIR * (SRB / RPT);
@@ -522,7 +525,7 @@ static int launch_t2d(const CUtensorMap& mT, const CUtensorMap& mC, const T2Para
         IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    const int slots = igg::sm_count() * (SRB == 4 ? 4 : (SRB == 8 ? 2 : 1));   // small blocks: several CTAs per SM
+    const int slots = igg::sm_count() * (SRB == 4 ? IGG_T2_CTAS_SRB4 : (SRB == 8 ? 2 : 1));   // small blocks: several CTAs per SM
     const int nitems = num_items(p.g);
     const int grid = nitems < slots ? nitems : slots;
     if (grid > 1024) {

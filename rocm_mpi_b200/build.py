@@ -67,6 +67,34 @@ def _compile(src: str, force: bool, verbose: bool, hdr_m: float) -> str:
     return obj
 
 
+def build_variant(name: str, defines: List[str]) -> str:
+    """Compile-time variant of the library for A/B runs: ``_lib/libigg_b200_<name>.so`` built with extra ``-D``
+    flags into its own object directory (load it with ``IGG_B200_LIB=<path>``)."""
+    obj_dir = os.path.join(ROOT, "build", "obj_" + name)
+    os.makedirs(obj_dir, exist_ok=True)
+    os.makedirs(LIBDIR, exist_ok=True)
+    objs = []
+    for src in sources():
+        obj = os.path.join(obj_dir, os.path.basename(src) + ".o")
+        if src.endswith(".cpp"):
+            cmd = [nvcc(), *ARCH, "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off",
+                   "-Xcompiler", "-fopenmp", "-I", INC, *defines, "-c", src, "-o", obj]
+        else:
+            cmd = [nvcc(), *ARCH, *NVCC_FLAGS, *defines, "-c", src, "-o", obj]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        with open(obj + ".log", "w") as f:
+            f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
+        objs.append(obj)
+    lib = os.path.join(LIBDIR, f"libigg_b200_{name}.so")
+    r = subprocess.run([nvcc(), *ARCH, "-shared", "-cudart", "static", "-Xcompiler", "-fopenmp", "-o", lib, *objs],
+                       capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    return lib
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     os.makedirs(LIBDIR, exist_ok=True)
@@ -96,5 +124,10 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--variant", default=None, help="name of a compile-time variant to build next to the default library")
+    ap.add_argument("-D", dest="defs", action="append", default=[], help="extra define for --variant, e.g. -D IGG_T2_CTAS_SRB4=5")
     a = ap.parse_args()
-    print(build(a.force, a.verbose))
+    if a.variant:
+        print(build_variant(a.variant, ["-D" + d for d in a.defs]))
+    else:
+        print(build(a.force, a.verbose))

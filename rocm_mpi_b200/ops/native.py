@@ -13,7 +13,9 @@ from typing import Optional, Sequence
 
 import torch
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_lib", "libigg_b200.so")
+# IGG_B200_LIB: load another build of the library (A/B runs of compile-time variants); default = the in-tree build
+_LIB_PATH = os.environ.get("IGG_B200_LIB") or os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                                            "_lib", "libigg_b200.so")
 _lib = None
 _load_error: Optional[str] = None
 
