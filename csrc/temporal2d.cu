@@ -90,9 +90,28 @@ __device__ __forceinline__ void mbar_arrive_u32(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
-struct T2Acc {            // running diagnostics of a thread
-    double d1max, d1sum, d2max, d2sum;
+// Diagnostics {max1, sum1, max2, sum2}: a thread accumulates over ONE work item in registers; at the end of the item
+// the warp folds its lanes and lane 0 merges the result into the warp's own slot in shared memory (no other warp
+// touches it).  Nothing diagnostic is carried in registers from item to item.
+struct T2Acc {
+    double* slot;         // [4] doubles of this warp, stride T2_ACC_STRIDE
 };
+constexpr int T2_ACC_STRIDE = 32;
+__device__ __forceinline__ void t2_flush_diag(const T2Acc& acc, double m1, double s1, double m2, double s2) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        m1 = igg::max_fast(m1, __shfl_xor_sync(0xffffffffu, m1, off));
+        s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+        m2 = igg::max_fast(m2, __shfl_xor_sync(0xffffffffu, m2, off));
+        s2 += __shfl_xor_sync(0xffffffffu, s2, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        acc.slot[0 * T2_ACC_STRIDE] = igg::max_fast(acc.slot[0 * T2_ACC_STRIDE], m1);
+        acc.slot[1 * T2_ACC_STRIDE] += s1;
+        acc.slot[2 * T2_ACC_STRIDE] = igg::max_fast(acc.slot[2 * T2_ACC_STRIDE], m2);
+        acc.slot[3 * T2_ACC_STRIDE] += s2;
+    }
+}
 
 // Step 1 of one block for one thread: mid rows rg*RPT ... rg*RPT+RPT-1.  EDGE = the block may contain rows outside the
 // item's own output range [x_lo, x_hi] (first block and the last two): only then are rows tested one by one.
@@ -156,7 +175,7 @@ template <int SRB, int RPT, bool DIAG>
 __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict__ T2, int ny, const Phys& ph1,
                                               const Phys& ph2, uint32_t sT, uint32_t sC, uint32_t sM, uint32_t fullT,
                                               uint32_t emptyT, uint32_t fullC, uint32_t emptyC, unsigned tq, unsigned cq,
-                                              unsigned mq, int cp, int rg, int consumers, T2Acc& acc) {
+                                              unsigned mq, int cp, int rg, int consumers, const T2Acc& acc) {
     constexpr int NRG = SRB / RPT;
     constexpr uint32_t ROWB = BW * 8, BLKB = SRB * ROWB;
     const uint32_t colB = (uint32_t)cp * 16u;
@@ -224,19 +243,24 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
         mbar_arrive_u32(emptyT + tprev * 8);
         mbar_arrive_u32(emptyC + cprev * 8);
     }
-    if (DIAG && pair_ok) {
-        acc.d1max = igg::max_fast(acc.d1max, i1max);
-        acc.d1sum += i1sum;
-        acc.d2max = igg::max_fast(acc.d2max, i2max);
-        acc.d2sum += i2sum;
-    }
+    if (DIAG)
+        t2_flush_diag(acc, pair_ok ? i1max : -INFINITY, pair_ok ? i1sum : 0.0, pair_ok ? i2max : -INFINITY,
+                      pair_ok ? i2sum : 0.0);
 }
 
-template <int SRB, int RPT, bool DIAG>
+// Resident CTAs per SM.  With 4-row blocks a CTA has 5 warps (4 consumer warps + the producer): four CTAs put 5 warps
+// on each of the SM's four schedulers (<= 102 registers per thread), five CTAs put 7 on one of them, which caps a
+// thread at 72 registers (each scheduler owns a quarter of the register file).  The plain kernel fits (0.534 vs
+// 0.547 ms per step, measured in one call); the kernel with the in-kernel diagnostics does not without spilling in
+// its inner loop, so it stays at four.
 #ifndef IGG_T2_CTAS_SRB4
-#define IGG_T2_CTAS_SRB4 4      // resident CTAs per SM with 4-row blocks (40 KB of shared memory, 160 threads each)
+#define IGG_T2_CTAS_SRB4 5
 #endif
-__global__ void __launch_bounds__(NPAIR*(SRB / RPT) + 32, SRB == 4 ? IGG_T2_CTAS_SRB4 : (SRB == 8 ? 2 : 1))
+constexpr int t2_ctas_per_sm(int srb, bool diag) {
+    return srb == 4 ? (diag ? 4 : IGG_T2_CTAS_SRB4) : (srb == 8 ? 2 : 1);
+}
+template <int SRB, int RPT, bool DIAG>
+__global__ void __launch_bounds__(NPAIR*(SRB / RPT) + 32, t2_ctas_per_sm(SRB, DIAG))
 diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapC,
                         const __grid_constant__ T2Params p) {
     constexpr int CONSUMERS = NPAIR * (SRB / RPT);
@@ -312,7 +336,16 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         ph2.lam = p.dev_params[4]; ph2.dt = p.dev_params[5]; ph2._dx = p.dev_params[6]; ph2._dy = p.dev_params[7];
     }
     constexpr bool diag = DIAG;
-    double d1max = -INFINITY, d1sum = 0.0, d2max = -INFINITY, d2sum = 0.0;
+    __shared__ double wacc[DIAG ? 4 * T2_ACC_STRIDE : 1];      // [max1 | sum1 | max2 | sum2][warp]
+    T2Acc acc;
+    acc.slot = &wacc[DIAG ? (tid >> 5) : 0];
+    if (DIAG && (tid & 31) == 0) {
+        acc.slot[0 * T2_ACC_STRIDE] = -INFINITY;
+        acc.slot[1 * T2_ACC_STRIDE] = 0.0;
+        acc.slot[2 * T2_ACC_STRIDE] = -INFINITY;
+        acc.slot[3 * T2_ACC_STRIDE] = 0.0;
+    }
+    __syncwarp();
     unsigned tq = 0, cq = 0, mq = 0;
     const uint32_t sT = smem_u32(ringT), sC = smem_u32(ringC), sM = smem_u32(ringM);
     const uint32_t aFullT = smem_u32(fullT), aEmptyT = smem_u32(emptyT), aFullC = smem_u32(fullC),
@@ -326,16 +359,15 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;      // inside [1, nx-2] by construction
         const bool inner = item_is_inner(p.g, it);
         if (inner && p.lean) {
-            T2Acc acc = {d1max, d1sum, d2max, d2sum};
             t2_inner_item<SRB, RPT, DIAG>(it, p.T2, ny, ph1, ph2, sT, sC, sM, aFullT, aEmptyT, aFullC, aEmptyC, tq, cq,
                                           mq, cp, rg, CONSUMERS, acc);
-            d1max = acc.d1max; d1sum = acc.d1sum; d2max = acc.d2max; d2sum = acc.d2sum;
             tq += it.nbi;
             cq += it.nbi;
             mq += it.nbi;
             continue;
         }
         const int y = it.yb + 2 * cp;
+        double d1max = -INFINITY, d1sum = 0.0, d2max = -INFINITY, d2sum = 0.0;      // of this item
         mbar_wait(&fullT[tq % SNT], (tq / SNT) & 1);
         for (int b = 0; b < it.nbi; ++b) {
             const unsigned qb = tq + b, qc = cq + b;
@@ -393,6 +425,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         tq += it.nbi;
         cq += it.nbi;
         mq += it.nbi;
+        if (diag) t2_flush_diag(acc, d1max, d1sum, d2max, d2sum);
         if (edge_tile) {
             consumer_sync(CONSUMERS);   // every remote store of this item has been issued
             if (tid == 0) signal_edges_2d(p.push, p.edge_tiles, e_xl, e_xh, e_yl, e_yh);
@@ -403,7 +436,10 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
     if (diag) {
         __shared__ double red[4][32];
         __shared__ bool is_last;
-        double v[4] = {d1max, d1sum, d2max, d2sum};
+        __syncwarp();
+        const bool l0 = (tid & 31) == 0;
+        double v[4] = {l0 ? acc.slot[0 * T2_ACC_STRIDE] : -INFINITY, l0 ? acc.slot[1 * T2_ACC_STRIDE] : 0.0,
+                       l0 ? acc.slot[2 * T2_ACC_STRIDE] : -INFINITY, l0 ? acc.slot[3 * T2_ACC_STRIDE] : 0.0};
         auto block_fold = [&]() {
 #pragma unroll
             for (int q = 0; q < 4; ++q)
@@ -525,7 +561,7 @@ static int launch_t2d(const CUtensorMap& mT, const CUtensorMap& mC, const T2Para
         IGG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    const int slots = igg::sm_count() * (SRB == 4 ? IGG_T2_CTAS_SRB4 : (SRB == 8 ? 2 : 1));   // small blocks: several CTAs per SM
+    const int slots = igg::sm_count() * t2_ctas_per_sm(SRB, DIAG);   // small blocks: several CTAs per SM
     const int nitems = num_items(p.g);
     const int grid = nitems < slots ? nitems : slots;
     if (grid > 1024) {
