@@ -115,9 +115,25 @@ __device__ __forceinline__ void t2_flush_diag(const T2Acc& acc, double m1, doubl
 
 // Step 1 of one block for one thread: mid rows rg*RPT ... rg*RPT+RPT-1.  EDGE = the block may contain rows outside the
 // item's own output range [x_lo, x_hi] (first block and the last two): only then are rows tested one by one.
-template <int SRB, int RPT, bool DIAG, bool EDGE>
+// What an item on the array edge needs on top of an inner one (INNER = false): the boundary rules of step 1 (global
+// boundary keeps its value, halo cells take the neighbours' mid lines), per-cell column validity, and the push of the
+// new edge cells to the neighbours.
+struct T2Border {
+    int nx, ny;
+    int y;                 // global column of the thread's first cell
+    bool vy0, vy1;         // are the thread's two columns inside [1, ny-2]
+    bool pair_ok;          // not one of the box's two garbage column pairs
+    bool edge_tile;        // does this item push
+    bool e_xl, e_xh, e_yl, e_yh;
+    const MidLines* ml;
+    const igg_push2d* push;
+    const int* edge_tiles;
+};
+
+template <int SRB, int RPT, bool DIAG, bool EDGE, bool INNER>
 __device__ __forceinline__ void t2_lean_step1(uint32_t pa, uint32_t pb, uint32_t plast, uint32_t pc, uint32_t pm,
-                                              const Phys& ph1, int xr0, int x_lo, int x_hi, double& imax, double& isum) {
+                                              const Phys& ph1, int xr0, int x_lo, int x_hi, double& imax, double& isum,
+                                              const T2Border& bd) {
     constexpr uint32_t ROWB = BW * 8;
     d2 a = lds128(pa);
     d2 bb = lds128(pb);
@@ -127,13 +143,25 @@ __device__ __forceinline__ void t2_lean_step1(uint32_t pa, uint32_t pb, uint32_t
         const double bl = lds64(pb + r * ROWB - 8);
         const double br = lds64(pb + r * ROWB + 16);
         const d2 cc = lds128(pc + r * ROWB);
-        const double mA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph1);
-        const double mB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph1);
+        double mA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph1);
+        double mB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph1);
+        if (!INNER) {
+            const int xg = xr0 + r;
+            const bool vx = xg >= 1 && xg <= bd.nx - 2;
+            if (!(vx && bd.vy0)) mA = boundary_mid(*bd.ml, xg, bd.y, bd.nx, bd.ny, bb.x);
+            if (!(vx && bd.vy1)) mB = boundary_mid(*bd.ml, xg, bd.y + 1, bd.nx, bd.ny, bb.y);
+        }
         sts128(pm + r * ROWB, mA, mB);
         if (DIAG) {
-            if (!EDGE || (xr0 + r >= x_lo && xr0 + r <= x_hi)) {
-                imax = igg::max_fast(imax, igg::max_fast(mA, mB));
-                isum += mA + mB;
+            const bool row_ok = !EDGE || (xr0 + r >= x_lo && xr0 + r <= x_hi);
+            if (INNER) {
+                if (row_ok) {
+                    imax = igg::max_fast(imax, igg::max_fast(mA, mB));
+                    isum += mA + mB;
+                }
+            } else if (row_ok && bd.pair_ok) {
+                if (bd.vy0) { imax = igg::max_fast(imax, mA); isum += mA; }
+                if (bd.vy1) { imax = igg::max_fast(imax, mB); isum += mB; }
             }
         }
         a = bb;
@@ -142,10 +170,10 @@ __device__ __forceinline__ void t2_lean_step1(uint32_t pa, uint32_t pb, uint32_t
 }
 
 // Step 2 of one block for one thread: output rows (xb - 1 + rg*RPT + r) from the mid rows around them.
-template <int SRB, int RPT, bool DIAG, bool EDGE>
+template <int SRB, int RPT, bool DIAG, bool EDGE, bool INNER>
 __device__ __forceinline__ void t2_lean_step2(uint32_t mm2, uint32_t mm1, uint32_t m0, uint32_t cm1, uint32_t c0,
                                               const Phys& ph2, double* __restrict__ out, int ny, bool pair_ok, int x,
-                                              int x_lo, int x_hi, double& imax, double& isum) {
+                                              int x_lo, int x_hi, double& imax, double& isum, const T2Border& bd) {
     constexpr uint32_t ROWB = BW * 8;
     d2 a = lds128(mm2);
     d2 bb = lds128(mm1);
@@ -159,11 +187,30 @@ __device__ __forceinline__ void t2_lean_step2(uint32_t mm2, uint32_t mm1, uint32
         const double oA = update_cell(bb.x, a.x, c.x, bl, bb.y, cc.x, ph2);
         const double oB = update_cell(bb.y, a.y, c.y, bb.x, br, cc.y, ph2);
         const bool row_ok = !EDGE || (x + r >= x_lo && x + r <= x_hi);
-        if (pair_ok && row_ok) st_cs_f64x2(out + (size_t)r * ny, oA, oB);
-        if (DIAG) {
-            if (row_ok) {
-                imax = igg::max_fast(imax, igg::max_fast(oA, oB));
-                isum += oA + oB;
+        if (INNER) {
+            if (pair_ok && row_ok) st_cs_f64x2(out + (size_t)r * ny, oA, oB);
+            if (DIAG) {
+                if (row_ok) {
+                    imax = igg::max_fast(imax, igg::max_fast(oA, oB));
+                    isum += oA + oB;
+                }
+            }
+        } else {
+            const bool wa = row_ok && pair_ok && bd.vy0, wb = row_ok && pair_ok && bd.vy1;
+            double* o = out + (size_t)r * ny;
+            if (wa && wb) {
+                st_cs_f64x2(o, oA, oB);
+            } else {
+                if (wa) st_cs_f64(o, oA);
+                if (wb) st_cs_f64(o + 1, oB);
+            }
+            if (bd.edge_tile) {
+                if (wa) push_cell_2d(*bd.push, bd.nx, bd.ny, x + r, bd.y, oA);
+                if (wb) push_cell_2d(*bd.push, bd.nx, bd.ny, x + r, bd.y + 1, oB);
+            }
+            if (DIAG) {
+                if (wa) { imax = igg::max_fast(imax, oA); isum += oA; }
+                if (wb) { imax = igg::max_fast(imax, oB); isum += oB; }
             }
         }
         a = bb;
@@ -171,11 +218,12 @@ __device__ __forceinline__ void t2_lean_step2(uint32_t mm2, uint32_t mm1, uint32
     }
 }
 
-template <int SRB, int RPT, bool DIAG>
-__device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict__ T2, int ny, const Phys& ph1,
-                                              const Phys& ph2, uint32_t sT, uint32_t sC, uint32_t sM, uint32_t fullT,
-                                              uint32_t emptyT, uint32_t fullC, uint32_t emptyC, unsigned tq, unsigned cq,
-                                              unsigned mq, int cp, int rg, int consumers, const T2Acc& acc) {
+template <int SRB, int RPT, bool DIAG, bool INNER>
+__device__ __forceinline__ void t2_lean_item(const Item& it, double* __restrict__ T2, int ny, const Phys& ph1,
+                                             const Phys& ph2, uint32_t sT, uint32_t sC, uint32_t sM, uint32_t fullT,
+                                             uint32_t emptyT, uint32_t fullC, uint32_t emptyC, unsigned tq, unsigned cq,
+                                             unsigned mq, int cp, int rg, int consumers, const T2Acc& acc,
+                                             const T2Border& bd) {
     constexpr int NRG = SRB / RPT;
     constexpr uint32_t ROWB = BW * 8, BLKB = SRB * ROWB;
     const uint32_t colB = (uint32_t)cp * 16u;
@@ -199,7 +247,9 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
         const uint32_t tn = (ts + 1) & (SNT - 1);
         const uint32_t tnph = tn == 0 ? tph ^ 1u : tph;
         const bool has_next = b + 1 < it.nbi;
-        const bool edge = b == 0 || b + 2 >= it.nbi;       // rows outside [x_lo, x_hi] exist only in these blocks
+        // rows outside [x_lo, x_hi] exist only in the first block and the last two (items on the array edge test
+        // every row: their blocks are few)
+        const bool edge = !INNER || b == 0 || b + 2 >= it.nbi;
         if (has_next) mbar_wait_u32(fullT + tn * 8, tnph);
         mbar_wait_u32(fullC + cs * 8, cph);
         const uint32_t tc = sT + ts * BLKB, tp = sT + tprev * BLKB, tnx = sT + (has_next ? tn : ts) * BLKB;
@@ -211,9 +261,9 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
             const uint32_t pa = rg == 0 ? tp + (SRB - 1) * ROWB + colB : pb - ROWB;
             const uint32_t plast = rg == NRG - 1 ? tnx + colB : pb + RPT * ROWB;
             if (edge)
-                t2_lean_step1<SRB, RPT, DIAG, true>(pa, pb, plast, cc_ + myB, mc + myB, ph1, x + 1, x_lo, x_hi, i1max, i1sum);
+                t2_lean_step1<SRB, RPT, DIAG, true, INNER>(pa, pb, plast, cc_ + myB, mc + myB, ph1, x + 1, x_lo, x_hi, i1max, i1sum, bd);
             else
-                t2_lean_step1<SRB, RPT, DIAG, false>(pa, pb, plast, cc_ + myB, mc + myB, ph1, x + 1, x_lo, x_hi, i1max, i1sum);
+                t2_lean_step1<SRB, RPT, DIAG, false, true>(pa, pb, plast, cc_ + myB, mc + myB, ph1, x + 1, x_lo, x_hi, i1max, i1sum, bd);
         }
         __syncwarp();
         if (lane0 && b > 0) mbar_arrive_u32(emptyT + tprev * 8);      // T block b-1 is done
@@ -225,9 +275,9 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
             const uint32_t mm2 = rg == 0 ? mp + (SRB - 2) * ROWB + colB : m0 - 2 * ROWB;   // row rg*RPT - 2
             const uint32_t cm1 = rg == 0 ? cpv + (SRB - 1) * ROWB + colB : cc_ + myB - ROWB;
             if (edge)
-                t2_lean_step2<SRB, RPT, DIAG, true>(mm2, mm1, m0, cm1, cc_ + myB, ph2, out, ny, pair_ok, x, x_lo, x_hi, i2max, i2sum);
+                t2_lean_step2<SRB, RPT, DIAG, true, INNER>(mm2, mm1, m0, cm1, cc_ + myB, ph2, out, ny, pair_ok, x, x_lo, x_hi, i2max, i2sum, bd);
             else
-                t2_lean_step2<SRB, RPT, DIAG, false>(mm2, mm1, m0, cm1, cc_ + myB, ph2, out, ny, pair_ok, x, x_lo, x_hi, i2max, i2sum);
+                t2_lean_step2<SRB, RPT, DIAG, false, true>(mm2, mm1, m0, cm1, cc_ + myB, ph2, out, ny, pair_ok, x, x_lo, x_hi, i2max, i2sum, bd);
         }
         __syncwarp();
         if (lane0 && b > 0) mbar_arrive_u32(emptyC + cprev * 8);      // Cp block b-1 is done
@@ -243,9 +293,14 @@ __device__ __forceinline__ void t2_inner_item(const Item& it, double* __restrict
         mbar_arrive_u32(emptyT + tprev * 8);
         mbar_arrive_u32(emptyC + cprev * 8);
     }
-    if (DIAG)
-        t2_flush_diag(acc, pair_ok ? i1max : -INFINITY, pair_ok ? i1sum : 0.0, pair_ok ? i2max : -INFINITY,
-                      pair_ok ? i2sum : 0.0);
+    if (DIAG) {
+        const bool keep = !INNER || pair_ok;       // items on the edge have masked cell by cell already
+        t2_flush_diag(acc, keep ? i1max : -INFINITY, keep ? i1sum : 0.0, keep ? i2max : -INFINITY, keep ? i2sum : 0.0);
+    }
+    if (!INNER && bd.edge_tile) {
+        consumer_sync(consumers);   // every remote store of this item has been issued
+        if (threadIdx.x == 0) signal_edges_2d(*bd.push, bd.edge_tiles, bd.e_xl, bd.e_xh, bd.e_yl, bd.e_yh);
+    }
 }
 
 // Resident CTAs per SM.  With 4-row blocks a CTA has 5 warps (4 consumer warps + the producer): four CTAs put 5 warps
@@ -358,9 +413,24 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         const bool edge_tile = p.has_push && (e_xl || e_xh || e_yl || e_yh);
         const int x_lo = it.x0, x_hi = it.x0 + it.rows_out - 1;      // inside [1, nx-2] by construction
         const bool inner = item_is_inner(p.g, it);
-        if (inner && p.lean) {
-            t2_inner_item<SRB, RPT, DIAG>(it, p.T2, ny, ph1, ph2, sT, sC, sM, aFullT, aEmptyT, aFullC, aEmptyC, tq, cq,
-                                          mq, cp, rg, CONSUMERS, acc);
+        if (p.lean) {
+            T2Border bd;
+            bd.nx = nx; bd.ny = ny;
+            bd.y = it.yb + 2 * cp;
+            bd.vy0 = bd.y >= 1 && bd.y <= ny - 2;
+            bd.vy1 = bd.y + 1 >= 1 && bd.y + 1 <= ny - 2;
+            bd.pair_ok = cp >= 1 && cp <= NPAIR - 2;
+            bd.edge_tile = edge_tile;
+            bd.e_xl = e_xl; bd.e_xh = e_xh; bd.e_yl = e_yl; bd.e_yh = e_yh;
+            bd.ml = &p.ml;
+            bd.push = &p.push;
+            bd.edge_tiles = p.edge_tiles;
+            if (inner)
+                t2_lean_item<SRB, RPT, DIAG, true>(it, p.T2, ny, ph1, ph2, sT, sC, sM, aFullT, aEmptyT, aFullC, aEmptyC,
+                                                   tq, cq, mq, cp, rg, CONSUMERS, acc, bd);
+            else
+                t2_lean_item<SRB, RPT, DIAG, false>(it, p.T2, ny, ph1, ph2, sT, sC, sM, aFullT, aEmptyT, aFullC, aEmptyC,
+                                                    tq, cq, mq, cp, rg, CONSUMERS, acc, bd);
             tq += it.nbi;
             cq += it.nbi;
             mq += it.nbi;
