@@ -51,6 +51,7 @@ def parse_args():
     p.add_argument("--nx", type=int, default=16384)
     p.add_argument("--ny", type=int, default=16384)
     p.add_argument("--b-width", type=int, nargs=2, default=[16, 4])
+    p.add_argument("--dims", type=int, nargs=2, default=[0, 0], help="force the process grid (default: balanced, 8 -> 4x2)")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-verify", action="store_true")
     p.add_argument("--no-baseline", action="store_true")
@@ -311,7 +312,7 @@ def main() -> int:
     W = max(3, a.warmup)
     K = max(1, a.steps)
     nx, ny = a.nx, a.ny
-    me, dims, nprocs, coords, _ = igg.init_global_grid(nx, ny, 1, quiet=True)
+    me, dims, nprocs, coords, _ = igg.init_global_grid(nx, ny, 1, dimx=a.dims[0], dimy=a.dims[1], quiet=True)
     g = igg.global_grid()
     mode, variant, transport = IMPLS[a.impl]
     if a.impl == "ours":
@@ -327,9 +328,9 @@ def main() -> int:
         if not ver["ok"] and mode == "temporal":
             fallback = {"mode": "temporal", "verify": ver}
             mode = "fused"
-            igg.init_global_grid(nx, ny, 1, quiet=True, init_dist=False)
+            igg.init_global_grid(nx, ny, 1, dimx=dims[0], dimy=dims[1], quiet=True, init_dist=False)
             ver = verify(igg, Diffusion2D, torch, nx, ny, mode, dims, nprocs)
-        igg.init_global_grid(nx, ny, 1, quiet=True, init_dist=False)
+        igg.init_global_grid(nx, ny, 1, dimx=dims[0], dimy=dims[1], quiet=True, init_dist=False)
         g = igg.global_grid()
     steps_per_pass = 2 if mode == "temporal" else 1
     s = Diffusion2D(nx, ny, mode=mode, variant=variant, transport=transport, b_width=a.b_width)

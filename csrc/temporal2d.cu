@@ -197,12 +197,19 @@ struct T2Border {
     const MidLines* ml;
     const igg_push2d* push;
     const int* edge_tiles;
+    // One of the thread's two columns may be a y-halo column with a neighbour (y == 0: cell A, y == ny-1: cell B): its
+    // step-(k+1) value comes from the neighbour's mid line, one global load per row.  Loaded when needed it would
+    // stall the thread -- and, through the per-block barrier, its whole CTA -- for a memory latency in every block
+    // (measured with a y-periodic self-neighbour: +18 us per pass), so the values of block b+1 are requested
+    // during block b and carried in registers.
+    const double* yline;   // ml->ylo or ml->yhi for this thread, or NULL
+    bool yline_B;          // the halo column is the thread's second cell
 };
 
 template <int SRB, int RPT, bool DIAG, bool EDGE, bool INNER>
 __device__ __forceinline__ void t2_lean_step1(uint32_t pa, uint32_t pb, uint32_t plast, uint32_t pc, uint32_t pm,
                                               const Phys& ph1, int xr0, int x_lo, int x_hi, double& imax, double& isum,
-                                              const T2Border& bd) {
+                                              const T2Border& bd, const double* ymid = nullptr) {
     constexpr uint32_t ROWB = BW * 8;
     d2 a = lds128(pa);
     d2 bb = lds128(pb);
@@ -217,8 +224,14 @@ __device__ __forceinline__ void t2_lean_step1(uint32_t pa, uint32_t pb, uint32_t
         if (!INNER) {
             const int xg = xr0 + r;
             const bool vx = xg >= 1 && xg <= bd.nx - 2;
-            if (!(vx && bd.vy0)) mA = boundary_mid(*bd.ml, xg, bd.y, bd.nx, bd.ny, bb.x);
-            if (!(vx && bd.vy1)) mB = boundary_mid(*bd.ml, xg, bd.y + 1, bd.nx, bd.ny, bb.y);
+            if (vx && bd.yline) {                 // y-halo column with a neighbour: the prefetched mid-line value
+                if (bd.yline_B) mB = ymid[r]; else mA = ymid[r];
+                if (bd.yline_B) { if (!bd.vy0) mA = boundary_mid(*bd.ml, xg, bd.y, bd.nx, bd.ny, bb.x); }
+                else            { if (!bd.vy1) mB = boundary_mid(*bd.ml, xg, bd.y + 1, bd.nx, bd.ny, bb.y); }
+            } else {
+                if (!(vx && bd.vy0)) mA = boundary_mid(*bd.ml, xg, bd.y, bd.nx, bd.ny, bb.x);
+                if (!(vx && bd.vy1)) mB = boundary_mid(*bd.ml, xg, bd.y + 1, bd.nx, bd.ny, bb.y);
+            }
         }
         sts128(pm + r * ROWB, mA, mB);
         if (DIAG) {
@@ -306,6 +319,18 @@ __device__ __forceinline__ void t2_lean_item(const Item& it, double* __restrict_
     // diagnostics of this item: folded without any per-cell column test (the two garbage column pairs of the box
     // accumulate garbage) and merged into the thread's running values at the end only where the pair is valid
     double i1max = -INFINITY, i1sum = 0.0, i2max = -INFINITY, i2sum = 0.0;
+    // mid-line values of my y-halo column for the rows of the current block (ymid) and of the next one (ynext)
+    double ymid[RPT], ynext[RPT];
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) ymid[r] = ynext[r] = 0.0;
+    auto fetch_yline = [&](int xrow0, double (&dst)[RPT]) {
+#pragma unroll
+        for (int r = 0; r < RPT; ++r) {
+            const int xg = xrow0 + r;
+            if (xg >= 1 && xg <= bd.nx - 2) dst[r] = ld_mid(bd.yline + xg);
+        }
+    };
+    if (!INNER && bd.yline) fetch_yline(it.xin0 + rg * RPT, ymid);
     // slots and parities of block 0
     uint32_t ts = tq % SNT, tph = (tq / SNT) & 1u;
     uint32_t cs = cq % SNC, cph = (cq / SNC) & 1u;
@@ -332,8 +357,9 @@ __device__ __forceinline__ void t2_lean_item(const Item& it, double* __restrict_
             const uint32_t pb = tc + myB;
             const uint32_t pa = rg == 0 ? tp + (SRB - 1) * ROWB + colB : pb - ROWB;
             const uint32_t plast = rg == NRG - 1 ? tnx + colB : pb + RPT * ROWB;
+            if (!INNER && bd.yline && has_next) fetch_yline(x + 1 + SRB, ynext);     // rows of block b+1
             if (edge)
-                t2_lean_step1<SRB, RPT, DIAG, true, INNER>(pa, pb, plast, cc_ + myB, mc + myB, ph1, x + 1, x_lo, x_hi, i1max, i1sum, bd);
+                t2_lean_step1<SRB, RPT, DIAG, true, INNER>(pa, pb, plast, cc_ + myB, mc + myB, ph1, x + 1, x_lo, x_hi, i1max, i1sum, bd, ymid);
             else
                 t2_lean_step1<SRB, RPT, DIAG, false, true>(pa, pb, plast, cc_ + myB, mc + myB, ph1, x + 1, x_lo, x_hi, i1max, i1sum, bd);
         }
@@ -367,6 +393,10 @@ __device__ __forceinline__ void t2_lean_item(const Item& it, double* __restrict_
         if (!SELF) {
             __syncwarp();
             if (lane0 && b > 0) mbar_arrive_u32(emptyC + cprev * 8);  // Cp block b-1 is done
+        }
+        if (!INNER) {
+#pragma unroll
+            for (int r = 0; r < RPT; ++r) ymid[r] = ynext[r];
         }
         // advance the rings
         tprev = ts; ts = tn; tph = tnph;
@@ -514,6 +544,10 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
             bd.ml = &p.ml;
             bd.push = &p.push;
             bd.edge_tiles = p.edge_tiles;
+            bd.yline = nullptr;
+            bd.yline_B = false;
+            if (bd.y == 0 && p.ml.ylo) bd.yline = p.ml.ylo;
+            if (bd.y + 1 == ny - 1 && p.ml.yhi) { bd.yline = p.ml.yhi; bd.yline_B = true; }
             if (inner)
                 t2_lean_item<SRB, RPT, DIAG, true>(it, p.T2, ny, ph1, ph2, sT, sC, sM, aFullT, aEmptyT, aFullC, aEmptyC,
                                                    tq, cq, mq, cp, rg, CONSUMERS, acc, bd);
@@ -729,6 +763,10 @@ diff2d_temporal2_sf_kernel(const __grid_constant__ CUtensorMap mapT, const __gri
         bd.ml = &p.ml;
         bd.push = &p.push;
         bd.edge_tiles = p.edge_tiles;
+        bd.yline = nullptr;
+        bd.yline_B = false;
+        if (bd.y == 0 && p.ml.ylo) bd.yline = p.ml.ylo;
+        if (bd.y + 1 == ny - 1 && p.ml.yhi) { bd.yline = p.ml.yhi; bd.yline_B = true; }
         if (item_is_inner(p.g, it))
             t2_lean_item<SRB, RPT, DIAG, true, true>(it, p.T2, ny, ph1, ph2, sT, sC, sM, aFullT, 0u, aFullC, 0u, tq, cq, mq,
                                                      cp, rg, CONSUMERS, acc, bd, &feed, &ccarry);
@@ -809,13 +847,13 @@ struct MidParams {
     uint64_t epoch;
 };
 
-// CTAs per face: one per 512 cells of the longer edge, at most 32 (a line is pure latency -- six dependent-free loads,
+// CTAs per face: one per 256 cells of the longer edge, at most 64 (a line is pure latency -- six dependent-free loads,
 // one remote store per cell -- so it is spread wide; the arrival counter is taken modulo this number, which depends
 // only on the field shape and is therefore the same for every launch of a time loop)
-constexpr int MID_MAX_CTAS_PER_FACE = 32;
+constexpr int MID_MAX_CTAS_PER_FACE = 64;
 static int mid_ctas_per_face(int nx, int ny) {
     const int n = nx > ny ? nx : ny;
-    int c = (n + 511) / 512;
+    int c = (n + 255) / 256;
     return c < 1 ? 1 : (c > MID_MAX_CTAS_PER_FACE ? MID_MAX_CTAS_PER_FACE : c);
 }
 
