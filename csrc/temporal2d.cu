@@ -330,13 +330,16 @@ __device__ __forceinline__ void t2_lean_item(const Item& it, double* __restrict_
             if (xg >= 1 && xg <= bd.nx - 2) dst[r] = ld_mid(bd.yline + xg);
         }
     };
-    if (!INNER && bd.yline) fetch_yline(it.xin0 + rg * RPT, ymid);
     // slots and parities of block 0
     uint32_t ts = tq % SNT, tph = (tq / SNT) & 1u;
     uint32_t cs = cq % SNC, cph = (cq / SNC) & 1u;
     uint32_t ms = mq % SNM;
     uint32_t tprev = ts, cprev = cs, mprev = (ms + SNM - 1) % SNM;
     mbar_wait_u32(fullT + ts * 8, tph);
+    // Only now: the first T block of the item was requested AFTER its mid flags had been acquired, so its arrival
+    // orders these loads behind the neighbours' mid-line stores (read earlier they can see the previous pass' lines:
+    // found on 4 GPUs with a CTA whose first item lies on a y face).
+    if (!INNER && bd.yline) fetch_yline(it.xin0 + rg * RPT, ymid);
     // output pointer of my first step-2 row of block 0 (rows xb - 1 + rg*RPT + r)
     int x = it.xin0 - 1 + rg * RPT;
     double* out = T2 + (size_t)x * ny + (it.yb + 2 * cp);
