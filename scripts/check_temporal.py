@@ -39,10 +39,13 @@ def kernel_alone():
     return worst
 
 
+DIMS = [0, 0]            # --dimx / --dimy: force the process grid (e.g. 1 x 2: neighbours in y only)
+
+
 def through_solver(nx, ny, periods, nsteps):
     out = {}
     for mode in ("fused", "temporal"):
-        igg.init_global_grid(nx, ny, 1, periodx=periods[0], periody=periods[1], quiet=True)
+        igg.init_global_grid(nx, ny, 1, dimx=DIMS[0], dimy=DIMS[1], periodx=periods[0], periody=periods[1], quiet=True)
         s = Diffusion2D(nx, ny, mode=mode)
         s.begin()
         s.step(nsteps)
@@ -107,7 +110,10 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--skip-timing", action="store_true")
     ap.add_argument("--timing-only", action="store_true")
+    ap.add_argument("--dimx", type=int, default=0)
+    ap.add_argument("--dimy", type=int, default=0)
     a = ap.parse_args()
+    DIMS[0], DIMS[1] = a.dimx, a.dimy
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     ok = True
