@@ -31,7 +31,8 @@ get_fabric().check_errors(0)
 # 2) solver modes against the single-domain / virtual oracle
 gx, gy = igg.nx_g(), igg.ny_g()
 results = {}
-for mode, variant, transport in (("fused", "tma", "peer"), ("fused", "direct", "peer"), ("hide", "tma", "peer"),
+for mode, variant, transport in (("fused", "tma", "peer"), ("temporal", "tma", "peer"), ("fused", "direct", "peer"),
+                                 ("hide", "tma", "peer"),
                                  ("plain", "tma", "nccl"), ("plain", "tma", "peer"), ("persistent", "direct", "peer"), ("resident", "direct", "peer")):
     s = Diffusion2D(nx, ny, mode=mode, variant=variant, transport=transport, b_width=(8, 4))
     T0 = s.T.cpu().clone()

@@ -13,8 +13,10 @@ nx, ny, px, py, nt = map(int, sys.argv[1:6])
 me, dims, nprocs, coords, comm = igg.init_global_grid(nx, ny, 1, periodx=px, periody=py, quiet=True)
 vg = igg.VirtualGrid((nx, ny), dims, (px, py))
 res = {}
-for mode in ("fused", "persistent", "resident", "hide"):
-    s = Diffusion2D(nx, ny, mode=mode, variant="tma" if mode in ("fused", "hide") else "direct", b_width=(4, 2))
+for mode in ("fused", "temporal", "persistent", "resident", "hide"):
+    if mode == "temporal" and ny % 2:
+        continue
+    s = Diffusion2D(nx, ny, mode=mode, variant="tma" if mode in ("fused", "hide", "temporal") else "direct", b_width=(4, 2))
     T0 = s.T.cpu().clone()
     s.begin()
     done = 0
