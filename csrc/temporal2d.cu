@@ -52,6 +52,7 @@ struct T2Params {
     const uint64_t* mid_flag[4];   // my mid flags, one per line (xlo, xhi, ylo, yhi); NULL = no neighbour
     int has_push;
     int lean;                      // 1: inner items take the lean path (IGG_T2_LEAN=0 switches it off for A/B runs)
+    int yprefetch;                 // 1: mid-line values of a y-halo column are requested one block ahead (IGG_T2_YPREFETCH)
     int edge_tiles[9];
     int side_nb[4];
     igg_push2d push;
@@ -549,8 +550,8 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
             bd.edge_tiles = p.edge_tiles;
             bd.yline = nullptr;
             bd.yline_B = false;
-            if (bd.y == 0 && p.ml.ylo) bd.yline = p.ml.ylo;
-            if (bd.y + 1 == ny - 1 && p.ml.yhi) { bd.yline = p.ml.yhi; bd.yline_B = true; }
+            if (p.yprefetch && bd.y == 0 && p.ml.ylo) bd.yline = p.ml.ylo;
+            if (p.yprefetch && bd.y + 1 == ny - 1 && p.ml.yhi) { bd.yline = p.ml.yhi; bd.yline_B = true; }
             if (inner)
                 t2_lean_item<SRB, RPT, DIAG, true>(it, p.T2, ny, ph1, ph2, sT, sC, sM, aFullT, aEmptyT, aFullC, aEmptyC,
                                                    tq, cq, mq, cp, rg, CONSUMERS, acc, bd);
@@ -768,8 +769,8 @@ diff2d_temporal2_sf_kernel(const __grid_constant__ CUtensorMap mapT, const __gri
         bd.edge_tiles = p.edge_tiles;
         bd.yline = nullptr;
         bd.yline_B = false;
-        if (bd.y == 0 && p.ml.ylo) bd.yline = p.ml.ylo;
-        if (bd.y + 1 == ny - 1 && p.ml.yhi) { bd.yline = p.ml.yhi; bd.yline_B = true; }
+        if (p.yprefetch && bd.y == 0 && p.ml.ylo) bd.yline = p.ml.ylo;
+        if (p.yprefetch && bd.y + 1 == ny - 1 && p.ml.yhi) { bd.yline = p.ml.yhi; bd.yline_B = true; }
         if (item_is_inner(p.g, it))
             t2_lean_item<SRB, RPT, DIAG, true, true>(it, p.T2, ny, ph1, ph2, sT, sC, sM, aFullT, 0u, aFullC, 0u, tq, cq, mq,
                                                      cp, rg, CONSUMERS, acc, bd, &feed, &ccarry);
@@ -996,6 +997,9 @@ extern "C" int igg_diffusion2d_step2(const double* T, double* T2, const double* 
         if (srb == 4) rpt = 2;
     }
     p.lean = lean;
+    static int yprefetch = -1;
+    if (yprefetch < 0) yprefetch = env_int_("IGG_T2_YPREFETCH", 1);
+    p.yprefetch = yprefetch;
     p.g = make_geom(nx, ny, srb, igg_temporal2d_default_rows(), push ? 1 : 0);
     p.ph.lam = lam; p.ph.dt = dt; p.ph._dx = _dx; p.ph._dy = _dy;
     p.dev_params = opts ? opts->dev_params : nullptr;
