@@ -361,7 +361,9 @@ def main() -> int:
     # ---- same-box baseline arms (BASELINE.json: separate stencil kernel + pack / NCCL p2p / unpack) ----------
     base = {}
     if not a.no_baseline and a.impl not in ("nccl", "nccl_tma"):
-        for name in ("nccl", "nccl_tma"):
+        # nccl / nccl_tma: the baseline BASELINE.json defines; plain_peer: the SAME serial structure (kernel, swap,
+        # update_halo) with this framework's one-launch peer-memory update_halo -- the public API against NCCL
+        for name in ("nccl", "nccl_tma", "plain_peer"):
             bm, bv, bt = IMPLS[name]
             sb = Diffusion2D(nx, ny, mode=bm, variant=bv, transport=bt if nprocs > 1 else "peer", b_width=a.b_width)
             bms, _, _ = time_steps(sb, g, W, K, native, torch)
