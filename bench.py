@@ -423,7 +423,8 @@ def main() -> int:
                                   "steps, so T_eff can exceed the copy bandwidth while the DRAM traffic does not")
                          if steps_per_pass > 1 else None},
             "vs_baseline_arms": ({"kind": "same-box baseline defined by BASELINE.json (separate stencil kernel + pack / "
-                                          "NCCL p2p / unpack), timed in this process; NOT the Julia reference",
+                                          "NCCL p2p / unpack), timed in this process; NOT the Julia reference.  plain_peer = the same serial "
+                                          "structure with this framework's one-launch peer-memory update_halo",
                                   **{k: {"ratio": round(value / v["value"], 4), **v} for k, v in base.items()}}
                                  if base else None),
             "verify": ver, "fallback_from": fallback,
