@@ -70,6 +70,33 @@ class ClockSampler:
     def __init__(self, gpu_index: int = 0):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
+        # nvidia-smi needs ~0.1-0.3 s to start (longer on an 8-GPU box), which can exceed a short timed region: an
+        # NVML thread in this process samples the same quantities every 5 ms from the first moment and is used when
+        # nvidia-smi delivered fewer than three samples
+        self._nvml_rows, self._nvml_stop, self._nvml_thread = [], False, None
+        try:
+            import threading
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+
+            def loop():
+                while not self._nvml_stop:
+                    try:
+                        self._nvml_rows.append((pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM),
+                                                pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM),
+                                                pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0,
+                                                get_reasons(h)))
+                    except Exception:
+                        pass
+                    time.sleep(0.005)
+            self._nvml = pynvml
+            self._nvml_thread = threading.Thread(target=loop, daemon=True)
+            self._nvml_thread.start()
+        except Exception:
+            self._nvml_thread = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}",
                                        "--format=csv,noheader,nounits", "-lms", "50"],
@@ -78,8 +105,11 @@ class ClockSampler:
             self.p = None
 
     def stop(self) -> dict:
-        if self.p is None:
+        if self.p is None and not self._nvml_rows:
+            self._nvml_stop = True
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        if self.p is None:
+            self.p = subprocess.Popen(["true"])
         time.sleep(0.15)
         self.p.terminate()
         try:
@@ -107,8 +137,24 @@ class ClockSampler:
             os.unlink(self.f.name)
         except OSError:
             pass
+        source = "nvidia-smi"
+        self._nvml_stop = True
+        if self._nvml_thread is not None:
+            self._nvml_thread.join(timeout=1)
+        if len(sm) < 3 and self._nvml_rows:
+            source = "nvml"
+            nv = self._nvml
+            bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown,
+                    "hw_thermal_slowdown": nv.nvmlClocksEventReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": nv.nvmlClocksEventReasonSwThermalSlowdown,
+                    "sw_power_cap": nv.nvmlClocksEventReasonSwPowerCap}
+            sm = [float(r[0]) for r in self._nvml_rows]
+            mx = [float(r[1]) for r in self._nvml_rows]
+            pw = [float(r[2]) for r in self._nvml_rows]
+            reasons = {n for r in self._nvml_rows for n, b in bits.items() if r[3] & b}
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "source": source,
+                "reasons": sorted(reasons)}
 
 
 class NvlinkCounters:
