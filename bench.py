@@ -370,7 +370,18 @@ def main() -> int:
     #      timed instead and the line says so (`fallback_from`).
     ver, fallback = None, None
     if not a.no_verify and mode in ("fused", "temporal", "hide"):
-        ver = verify(igg, Diffusion2D, torch, nx, ny, mode, dims, nprocs)
+        try:
+            ver = verify(igg, Diffusion2D, torch, nx, ny, mode, dims, nprocs)
+        except Exception as ex:                       # a failing check must not cost the run its line
+            if mode != "temporal":
+                raise
+            print(f"bench.py: verification of the two-step kernel raised {type(ex).__name__}: {ex}", file=sys.stderr)
+            ver = {"ok": False, "exception": f"{type(ex).__name__}: {ex}"[:300]}
+            if igg.grid_is_initialized():
+                try:
+                    igg.finalize_global_grid(finalize_dist=False)
+                except Exception:
+                    pass
         if not ver["ok"] and mode == "temporal":
             fallback = {"mode": "temporal", "verify": ver}
             mode = "fused"
