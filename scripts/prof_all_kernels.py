@@ -15,9 +15,13 @@ from rocm_mpi_b200.utils.output import inferno_lut
 dev = "cuda"
 # --- 2-D kernels at 8192 x 8192, periodic so that the push / flag paths are live
 igg.init_global_grid(8192, 8192, 1, periodx=1, periody=1, quiet=True, init_dist=False)
-for mode in ("fused", "hide", "plain"):
+for mode in ("fused", "hide", "plain", "temporal"):
     s = Diffusion2D(8192, 8192, mode=mode, variant="tma", transport="peer")
     s.begin(); s.step(2); s.finish()
+    if mode == "temporal":
+        s.step_controlled_pair()                     # the variant with the in-kernel diagnostics
+        s.finish()
+    s.close()
 s = Diffusion2D(8192, 8192, mode="fused", variant="direct")
 s.begin(); s.step(1); s.finish()
 T = s.T
@@ -32,6 +36,8 @@ native.update2d(T, dT, 1e-6)
 buf = torch.empty(nx, dtype=torch.float64, device=dev)
 native.pack_plane(T, 1, 1, buf); native.unpack_plane(T, 1, 0, buf)
 native.extract_inner(T)
+from rocm_mpi_b200.parallel.gather import gather_interior_device
+gather_interior_device(T)
 native.reduce_max_sum(T.view(-1))
 native.colormap(T, 0.0, 1.0, torch.from_numpy(inferno_lut()))
 native.gaussian_ic_2d(T, 0.0, 0.0, 1e-3, 1e-3, 10.0, 10.0)
