@@ -114,6 +114,68 @@ __device__ __forceinline__ void t2_flush_diag(const T2Acc& acc, double m1, doubl
     }
 }
 
+// End of a kernel with diagnostics: every warp's slot -> CTA partial -> scratch; the last CTA (ticket) folds all
+// partials in a fixed order, restores a NaN that the hot loops' compare-select max dropped (it is still in the sum) and
+// re-arms the ticket.  THREADS = the threads that take part (the consumers: the whole CTA in the self-fed kernel).
+template <int THREADS>
+__device__ __forceinline__ void t2_diag_finish(DiagScratch2* scratch, double* diag_out, const T2Acc& acc) {
+    constexpr int NCW = THREADS / 32;
+    const int tid = threadIdx.x;
+    __shared__ double red[4][32];
+    __shared__ bool is_last;
+    __syncwarp();
+    const bool l0 = (tid & 31) == 0;
+    double v[4] = {l0 ? acc.slot[0 * T2_ACC_STRIDE] : -INFINITY, l0 ? acc.slot[1 * T2_ACC_STRIDE] : 0.0,
+                   l0 ? acc.slot[2 * T2_ACC_STRIDE] : -INFINITY, l0 ? acc.slot[3 * T2_ACC_STRIDE] : 0.0};
+    auto block_fold = [&]() {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
+                v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
+            }
+        if ((tid & 31) == 0)
+            for (int q = 0; q < 4; ++q) red[q][tid >> 5] = v[q];
+        consumer_sync(THREADS);
+        if (tid < 32) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                v[q] = tid < NCW ? red[q][tid] : ((q & 1) ? 0.0 : -INFINITY);
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) {
+                    const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
+                    v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
+                }
+            }
+        }
+        consumer_sync(THREADS);
+    };
+    block_fold();
+    if (tid == 0) {
+        for (int q = 0; q < 4; ++q) scratch->part[q][blockIdx.x] = v[q];
+        __threadfence();
+        is_last = atomicAdd(&scratch->ticket, 1u) == gridDim.x - 1;
+    }
+    consumer_sync(THREADS);
+    if (is_last) {
+        __threadfence();
+        for (int q = 0; q < 4; ++q) v[q] = (q & 1) ? 0.0 : -INFINITY;
+        for (unsigned int b2 = tid; b2 < gridDim.x; b2 += THREADS)
+            for (int q = 0; q < 4; ++q) {
+                const double o = scratch->part[q][b2];
+                v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
+            }
+        block_fold();
+        if (tid == 0) {
+            if (v[1] != v[1]) v[0] = v[1];
+            if (v[3] != v[3]) v[2] = v[3];
+            for (int q = 0; q < 4; ++q) diag_out[q] = v[q];
+            scratch->ticket = 0;
+        }
+    }
+}
+
 // Step 1 of one block for one thread: mid rows rg*RPT ... rg*RPT+RPT-1.  EDGE = the block may contain rows outside the
 // item's own output range [x_lo, x_hi] (first block and the last two): only then are rows tested one by one.
 // ---- self-fed pipeline ---------------------------------------------------------------------------------------
@@ -629,64 +691,7 @@ diff2d_temporal2_kernel(const __grid_constant__ CUtensorMap mapT, const __grid_c
         }
     }
 
-    // optional diagnostic: CTA partials -> scratch; the last CTA (ticket) folds all partials in a fixed order
-    if (diag) {
-        __shared__ double red[4][32];
-        __shared__ bool is_last;
-        __syncwarp();
-        const bool l0 = (tid & 31) == 0;
-        double v[4] = {l0 ? acc.slot[0 * T2_ACC_STRIDE] : -INFINITY, l0 ? acc.slot[1 * T2_ACC_STRIDE] : 0.0,
-                       l0 ? acc.slot[2 * T2_ACC_STRIDE] : -INFINITY, l0 ? acc.slot[3 * T2_ACC_STRIDE] : 0.0};
-        auto block_fold = [&]() {
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-#pragma unroll
-                for (int off = 16; off > 0; off >>= 1) {
-                    const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
-                    v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
-                }
-            if ((tid & 31) == 0)
-                for (int q = 0; q < 4; ++q) red[q][tid >> 5] = v[q];
-            consumer_sync(CONSUMERS);
-            if (tid < 32) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    v[q] = tid < NCW ? red[q][tid] : ((q & 1) ? 0.0 : -INFINITY);
-#pragma unroll
-                    for (int off = 16; off > 0; off >>= 1) {
-                        const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
-                        v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
-                    }
-                }
-            }
-            consumer_sync(CONSUMERS);
-        };
-        block_fold();
-        if (tid == 0) {
-            for (int q = 0; q < 4; ++q) p.diag->part[q][blockIdx.x] = v[q];
-            __threadfence();
-            is_last = atomicAdd(&p.diag->ticket, 1u) == gridDim.x - 1;
-        }
-        consumer_sync(CONSUMERS);
-        if (is_last) {
-            __threadfence();
-            for (int q = 0; q < 4; ++q) v[q] = (q & 1) ? 0.0 : -INFINITY;
-            for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS)
-                for (int q = 0; q < 4; ++q) {
-                    const double o = p.diag->part[q][b2];
-                    v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
-                }
-            block_fold();
-            if (tid == 0) {
-                // the hot loops fold with fmax (one instruction; it drops NaN): a NaN anywhere makes the SUM NaN,
-                // and then the max is reported as NaN too, like the reference's maximum(T_v)
-                if (v[1] != v[1]) v[0] = v[1];
-                if (v[3] != v[3]) v[2] = v[3];
-                for (int q = 0; q < 4; ++q) p.diag_out[q] = v[q];
-                p.diag->ticket = 0;
-            }
-        }
-    }
+    if (diag) t2_diag_finish<CONSUMERS>(p.diag, p.diag_out, acc);
 }
 
 // ---- the self-fed kernel ------------------------------------------------------------------------------------
@@ -781,61 +786,7 @@ diff2d_temporal2_sf_kernel(const __grid_constant__ CUtensorMap mapT, const __gri
         cq += it.nbi;
         mq += it.nbi;
     }
-    if (DIAG) {
-        __shared__ double red[4][32];
-        __shared__ bool is_last;
-        __syncwarp();
-        const bool l0 = (tid & 31) == 0;
-        double v[4] = {l0 ? acc.slot[0 * T2_ACC_STRIDE] : -INFINITY, l0 ? acc.slot[1 * T2_ACC_STRIDE] : 0.0,
-                       l0 ? acc.slot[2 * T2_ACC_STRIDE] : -INFINITY, l0 ? acc.slot[3 * T2_ACC_STRIDE] : 0.0};
-        auto block_fold = [&]() {
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-#pragma unroll
-                for (int off = 16; off > 0; off >>= 1) {
-                    const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
-                    v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
-                }
-            if ((tid & 31) == 0)
-                for (int q = 0; q < 4; ++q) red[q][tid >> 5] = v[q];
-            __syncthreads();
-            if (tid < 32) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    v[q] = tid < NCW ? red[q][tid] : ((q & 1) ? 0.0 : -INFINITY);
-#pragma unroll
-                    for (int off = 16; off > 0; off >>= 1) {
-                        const double o = __shfl_xor_sync(0xffffffffu, v[q], off);
-                        v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
-                    }
-                }
-            }
-            __syncthreads();
-        };
-        block_fold();
-        if (tid == 0) {
-            for (int q = 0; q < 4; ++q) p.diag->part[q][blockIdx.x] = v[q];
-            __threadfence();
-            is_last = atomicAdd(&p.diag->ticket, 1u) == gridDim.x - 1;
-        }
-        __syncthreads();
-        if (is_last) {
-            __threadfence();
-            for (int q = 0; q < 4; ++q) v[q] = (q & 1) ? 0.0 : -INFINITY;
-            for (unsigned int b2 = tid; b2 < gridDim.x; b2 += CONSUMERS)
-                for (int q = 0; q < 4; ++q) {
-                    const double o = p.diag->part[q][b2];
-                    v[q] = (q & 1) ? v[q] + o : igg::max_nan(v[q], o);
-                }
-            block_fold();
-            if (tid == 0) {
-                if (v[1] != v[1]) v[0] = v[1];
-                if (v[3] != v[3]) v[2] = v[3];
-                for (int q = 0; q < 4; ++q) p.diag_out[q] = v[q];
-                p.diag->ticket = 0;
-            }
-        }
-    }
+    if (DIAG) t2_diag_finish<CONSUMERS>(p.diag, p.diag_out, acc);
 }
 
 // ---- mid lines -------------------------------------------------------------------------------------------
