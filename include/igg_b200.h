@@ -168,7 +168,8 @@ int igg_diffusion2d_resident_ex(double* T, double* T2, const double* Cp, int nx,
  *                                       step-(k+2) edge cells are pushed into the neighbours' T2 and the DATA
  *                                       flag `epoch` is released as igg_diffusion2d_step does.
  * Both take the SAME push descriptor (one epoch per pass).  Sides are indexed x-low, x-high, y-low, y-high.
- * STATUS: compiled and checked through its host emulator (igg_cpu_temporal2d_*); not yet run on a GPU. */
+ * STATUS: the benchmarked path (GPU tests: tests/test_temporal_gpu.py; multi-GPU: bench.py's verify block); the host
+ * emulator igg_cpu_temporal2d_* executes the generic path's index code. */
 typedef struct igg_mid2d {
     const double* my_mid;           /* my mid-line buffer, 2*ny + 2*nx doubles: [xlo | xhi | ylo | yhi]      */
     double* peer_mid[4];            /* mid-line buffer of the neighbour on side s (peer-mapped); NULL = none */

@@ -253,7 +253,7 @@ def diffusion2d_step2(T2: torch.Tensor, T: torch.Tensor, Cp: torch.Tensor, lam: 
     :func:`diffusion2d_midlines` with the same descriptors first (``PushPlan.mid_lines()``).
     ``dev_params``: device tensor of 8 doubles (``[lam, dt, _dx, _dy]`` of step k+1, then of step k+2);
     ``diag_out``: device tensor of 4 doubles receiving ``[max, sum]`` of step k+1 and of step k+2.
-    Experimental: validated through the host emulator only (:func:`cpu_temporal2d_emulate`)."""
+    GPU-tested (``tests/test_temporal_gpu.py``); :func:`cpu_temporal2d_emulate` executes the same index code on the host."""
     lib = require()
     nx, ny = T.shape
     if T2.shape != T.shape or Cp.shape != T.shape:
