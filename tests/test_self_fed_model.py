@@ -105,3 +105,44 @@ def test_model_catches_requests_that_run_too_far_ahead():
     with pytest.raises(AssertionError):
         for seed in range(50):
             simulate(nblocks=40, nwarps=4, seed=seed, t_ahead=4)
+
+
+# ---- mid lines of a y-halo column: when may a consumer read them? ------------------------------------------------------
+def simulate_midline_reads(seed, read_after_first_block):
+    """One CTA starting an item that lies on a y face.  Actors: the NEIGHBOUR (writes the mid line, then releases its
+    flag), THREAD 0 (acquires the flag, then requests the item's first T block), the TMA engine (the block arrives some
+    time after the request) and a CONSUMER thread that prefetches the mid-line values of the item's first rows --
+    either as soon as it reaches the item (the bug found on 4 GPUs) or only after the first T block has arrived (the
+    fix: the arrival is ordered behind thread 0's acquire).  Returns True if the consumer saw the new line."""
+    rng = random.Random(seed)
+    line_new = flag = requested = arrived = False
+    consumer_value = None
+    consumer_at_item = False
+    for _ in range(10000):
+        actor = rng.choice(["neighbour", "thread0", "tma", "consumer"])
+        if actor == "neighbour":
+            if not line_new:
+                line_new = True                      # stores of the mid line (then fence + release)
+            elif not flag:
+                flag = True
+        elif actor == "thread0":
+            if flag and not requested:               # ld.acquire saw the flag: request the first T block
+                requested = True
+        elif actor == "tma":
+            if requested and not arrived and rng.random() < 0.5:
+                arrived = True
+        elif actor == "consumer" and consumer_value is None:
+            consumer_at_item = True
+            if read_after_first_block and not arrived:
+                continue                             # mbarrier wait on the first T block
+            consumer_value = "new" if line_new else "stale"
+        if consumer_value is not None:
+            break
+    assert consumer_at_item
+    return consumer_value == "new"
+
+
+def test_midline_prefetch_is_safe_only_behind_the_first_block():
+    assert all(simulate_midline_reads(seed, read_after_first_block=True) for seed in range(300))
+    assert not all(simulate_midline_reads(seed, read_after_first_block=False) for seed in range(300)), \
+        "the model must reproduce the early read that bench.py's verify block caught"
